@@ -1,0 +1,211 @@
+/*
+ * viekf_batch.h -- C ABI of the B200 batch engine for the VI-EKF filter core.
+ *
+ * The reference (byu-magicc/VI-EKF) has no FFI layer; its boundary is the public C++ surface of
+ * class vi_ekf::VIEKF (reference include/vi_ekf.h:243-337).  Every entry point below names the
+ * reference method it replaces.  All arithmetic is IEEE double; all matrices crossing the ABI are
+ * column-major like Eigen's default (reference include/vi_ekf.h:53-61).
+ *
+ * One handle = B independent filter instances with NUM_FEATURES = N (a compile-time constant in the
+ * reference, include/vi_ekf.h:39-48; a creation-time constant here) resident on one CUDA device.
+ * Calls on one handle must be serialised by the caller (the reference's ROS wrapper holds one mutex
+ * around every VIEKF call, src/vi_ekf_ros.cpp:173-175).  Host pointers are copied during the call.
+ *
+ * Return value: 0 = ok, <0 = VIEKF_ERR_*.  Per-filter outcomes use the reference's meas_result_t
+ * values bit for bit (include/vi_ekf.h:132-138).
+ */
+#ifndef VIEKF_BATCH_H
+#define VIEKF_BATCH_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* ---- index maps: reference include/vi_ekf.h:87-111 -------------------------------------------- */
+enum { VIEKF_xPOS = 0, VIEKF_xVEL = 3, VIEKF_xATT = 6, VIEKF_xB_A = 10, VIEKF_xB_G = 13, VIEKF_xMU = 16, VIEKF_xZ = 17 };
+enum { VIEKF_dxPOS = 0, VIEKF_dxVEL = 3, VIEKF_dxATT = 6, VIEKF_dxB_A = 9, VIEKF_dxB_G = 12, VIEKF_dxMU = 15, VIEKF_dxZ = 16 };
+#define VIEKF_MAX_X(N) (17 + 5 * (N))  /* reference include/vi_ekf.h:47 */
+#define VIEKF_MAX_DX(N) (16 + 3 * (N)) /* reference include/vi_ekf.h:48 */
+
+/* measurement_type_t: reference include/vi_ekf.h:113-125 (same numeric values) */
+typedef enum {
+  VIEKF_ACC = 0, VIEKF_ALT = 1, VIEKF_ATT = 2, VIEKF_POS = 3, VIEKF_VEL = 4, VIEKF_QZETA = 5,
+  VIEKF_FEAT = 6, VIEKF_PIXEL_VEL = 7, VIEKF_DEPTH = 8, VIEKF_INV_DEPTH = 9, VIEKF_TOTAL_MEAS = 10
+} viekf_meas_type;
+
+/* meas_result_t: reference include/vi_ekf.h:132-138 (same numeric values) */
+typedef enum {
+  VIEKF_MEAS_SUCCESS = 0, VIEKF_MEAS_GATED = 1, VIEKF_MEAS_NAN = 2, VIEKF_MEAS_INVALID = 3,
+  VIEKF_MEAS_NEW_FEATURE = 4,
+  VIEKF_MEAS_NONE = 255 /* event produced no meas_result_t (propagate, keep, ...) */
+} viekf_meas_result;
+
+enum {
+  VIEKF_OK = 0, VIEKF_ERR_ARG = -1, VIEKF_ERR_CUDA = -2, VIEKF_ERR_NODEVICE = -3, VIEKF_ERR_UNSUPPORTED = -4,
+  VIEKF_ERR_NOMEM = -5
+};
+
+/* Per-filter sticky flags (replace the reference's debug-only NAN_CHECK / NEGATIVE_DEPTH exits,
+ * include/vi_ekf.h:29-37, src/vi_ekf/vi_ekf_error.cpp). */
+enum {
+  VIEKF_FLAG_NAN_STATE = 1,       /* NaNsInTheHouse() would have fired */
+  VIEKF_FLAG_DEPTH_NAN_FIXED = 2, /* fix_depth: rho was NaN   (vi_ekf_helper.cpp:137-141) */
+  VIEKF_FLAG_DEPTH_NEG_FIXED = 4, /* fix_depth: rho < 0       (vi_ekf_helper.cpp:142-148) */
+  VIEKF_FLAG_DEPTH_BIG_FIXED = 8, /* fix_depth: rho > 100     (vi_ekf_helper.cpp:149-154) */
+  VIEKF_FLAG_NAN_GAIN = 16,       /* NO_NANS(K)&&NO_NANS(H) failed -> update skipped (vi_ekf_meas.cpp:247) */
+  VIEKF_FLAG_BACKWARD_DT = 32     /* "Trying to propagate backwards" (vi_ekf.cpp:285-289) */
+};
+
+/* Everything VIEKF::load reads from params/ekf.yaml (reference src/vi_ekf/vi_ekf.cpp:101-155) and the
+ * arguments of the 17-argument VIEKF::init (vi_ekf.cpp:64-99).  Quaternions are [w,x,y,z]. */
+typedef struct viekf_config {
+  double x0[17];
+  double P0[16];
+  double Qx[16];
+  double lambda[16];
+  double Qu[6];
+  double P0_feat[3];
+  double Qx_feat[3];
+  double lambda_feat[3];
+  double cam_center[2];
+  double focal_len[2];
+  double q_b_c[4];
+  double p_b_c[3];
+  double q_b_u[4];
+  double min_depth;
+  double keyframe_overlap_threshold;
+  int32_t use_drag_term;
+  int32_t use_partial_update;
+  int32_t use_keyframe_reset;
+  int32_t reserved;
+} viekf_config;
+
+/* Fills cfg with the values of the reference's params/ekf.yaml. */
+void viekf_config_default(viekf_config* cfg);
+
+/* ---- in-order event tape (replaces the rewind/replay queue, vi_ekf_meas.cpp:6-194) --- */
+typedef enum {
+  VIEKF_EV_PROP = 0,  /* propagate_state(u, t, false)                       vi_ekf.cpp:262-318 */
+  VIEKF_EV_UPD = 1,   /* add_measurement + update in order; a FEAT with an untracked id initialises the
+                         feature and returns MEAS_NEW_FEATURE                vi_ekf_meas.cpp:130-147,196-278 */
+  VIEKF_EV_INIT = 2,  /* init_feature(pixel, id, depth)                     vi_ekf_feat.cpp:6-47 */
+  VIEKF_EV_CLEAR = 3, /* clear_feature(id)                                  vi_ekf_feat.cpp:50-73 */
+  VIEKF_EV_KEEP = 4,  /* keep_only_features(ids)                            vi_ekf_feat.cpp:81-142 */
+  VIEKF_EV_STAT = 5,  /* accumulate error statistics against the truth carried in z (no reference
+                         counterpart; names from multirotor_sim/mclogger.h:50-52) */
+  VIEKF_EV_KFRESET = 6 /* keyframe_reset()                                   vi_ekf_kfr.cpp:56-157 */
+} viekf_event_kind;
+
+typedef struct viekf_event {
+  int32_t kind;   /* viekf_event_kind */
+  int32_t type;   /* UPD: viekf_meas_type */
+  int32_t id;     /* UPD/INIT/CLEAR: feature id (-1 none); STAT: bucket index */
+  int32_t active; /* UPD: the reference's `active` flag (vi_ekf_meas.cpp:230) */
+  int32_t zdim;   /* UPD: rows of z (4 for ATT/QZETA quaternions) */
+  int32_t rdim;   /* UPD: rows of the residual / R */
+  int32_t n_ids;  /* KEEP: number of ids */
+  int32_t ids_off;/* KEEP: offset into the tape's id pool */
+  int32_t noise;  /* >=0: index of the per-instance value block for this event (see viekf_tape), -1: z is shared */
+  int32_t pad;
+  double t;       /* PROP: absolute time of the IMU sample; others: informational */
+  double z[8];    /* PROP: u = [acc(3), gyro(3)] in the IMU frame; UPD: z[0..zdim), z[4] = depth (FEAT);
+                     INIT: pixel(2), z[4] = depth (NaN = unknown); STAT: true pos(3) vel(3) att(4)=10 -> see truth block */
+  double R[9];    /* UPD: rdim x rdim column-major */
+} viekf_event;
+
+/* A tape is shared by all B instances (same control flow, Monte-Carlo use).  Per-instance values, when
+ * present, live in `values`: instance b reads doubles values[b*values_stride + 8*noise + k], k<8, in place of
+ * event.z[k] (PROP: k<6, UPD: k<zdim, STAT: 16 true base-state entries are read from two consecutive blocks). */
+typedef struct viekf_tape {
+  const viekf_event* events;
+  int64_t n_events;
+  const int32_t* id_pool;
+  int64_t n_ids;
+  const double* values; /* host pointer, may be NULL */
+  int64_t values_stride; /* doubles per instance */
+} viekf_tape;
+
+/* Statistics accumulated by STAT events, per bucket (all sums over the filters of this handle):
+ * [0] count, [1..16] sum e, [17..32] sum e^2, [33] sum NEES16, [34] sum NEES6 (pos+att),
+ * [35] #gated updates so far, [36] #fix_depth interventions so far, [37..39] reserved.
+ * e = x_true [-] x_hat on the 16 base error states (reference boxminus, vi_ekf_helper.cpp:100-111). */
+#define VIEKF_STAT_WIDTH 40
+
+typedef struct viekf_batch viekf_batch; /* opaque */
+
+/* VIEKF::VIEKF() + init(...)/load(...) for B instances (vi_ekf.cpp:7-155). device = CUDA ordinal. */
+int viekf_batch_create(const viekf_config* cfg, int64_t B, int32_t N, int32_t device, viekf_batch** out);
+void viekf_batch_destroy(viekf_batch* h);
+const char* viekf_last_error(void);
+
+/* set_x0 / set_imu_bias generalised: overwrite the first 17 state entries of every instance
+ * (vi_ekf.cpp:157-160,180-184).  x0 is [17 x B] column-major (instance b at x0 + 17*b), or one column when
+ * broadcast != 0. */
+int viekf_batch_set_x0(viekf_batch* h, const double* x0, int32_t broadcast);
+/* Perturb every instance: x <- x [+] (sqrt(P0) .* n), n ~ N(0,1) from Philox(seed, instance). */
+int viekf_batch_perturb_x0(viekf_batch* h, uint64_t seed);
+
+/* get_state (vi_ekf.cpp:187-190): x is [MAX_X x count], instances first..first+count.  Only the live part
+ * x[0 : 17+5*len) is defined; dead entries are written as 0. */
+int viekf_batch_get_state(viekf_batch* h, int64_t first, int64_t count, double* x);
+/* get_covariance (vi_ekf.cpp:197-200): P is [MAX_DX x MAX_DX x count] column-major, reference ordering. */
+int viekf_batch_get_covariance(viekf_batch* h, int64_t first, int64_t count, double* P);
+/* get_len_features / tracked_features (include/vi_ekf.h:272,286): len[count], ids[N x count] (-1 padded). */
+int viekf_batch_get_features(viekf_batch* h, int64_t first, int64_t count, int32_t* len, int32_t* ids);
+/* sticky VIEKF_FLAG_* per filter, counters[3 x count] = {#gated, #fix_depth, #nan_gain}. */
+int viekf_batch_get_flags(viekf_batch* h, int64_t first, int64_t count, uint32_t* flags, uint32_t* counters);
+/* current filter time t_[i_] of each instance */
+int viekf_batch_get_time(viekf_batch* h, int64_t first, int64_t count, double* t);
+
+/* propagate_state(u, t, save_input) (vi_ekf.cpp:262-318).  u is [6 x B] (IMU frame), or one column when
+ * broadcast != 0.  The first call only latches the start time (vi_ekf.cpp:274-279). */
+int viekf_batch_propagate(viekf_batch* h, const double* u, int32_t broadcast, double t);
+
+/* In-order update(meas) (vi_ekf_meas.cpp:196-278) at the filters' current time, preceded by
+ * add_measurement's feature bookkeeping (vi_ekf_meas.cpp:136-147): z is [zdim x B] or one column when
+ * broadcast != 0; R is rdim x rdim column-major; result[B] receives meas_result_t per filter (may be NULL). */
+int viekf_batch_update(viekf_batch* h, int32_t type, const double* z, int32_t zdim, int32_t broadcast,
+                       const double* R, int32_t rdim, int32_t active, int32_t id, double depth,
+                       uint8_t* result);
+
+/* init_feature / clear_feature / keep_only_features (vi_ekf_feat.cpp:6-142), applied to every instance.
+ * pixel is [2 x B] or broadcast. ok[B] receives init_feature's bool (may be NULL). */
+int viekf_batch_init_feature(viekf_batch* h, const double* pixel, int32_t broadcast, int32_t id, double depth,
+                             uint8_t* ok);
+int viekf_batch_clear_feature(viekf_batch* h, int32_t id);
+int viekf_batch_keep_only_features(viekf_batch* h, const int32_t* ids, int32_t n);
+int viekf_batch_keyframe_reset(viekf_batch* h);
+
+/* Fused path: run a whole tape with x and P resident on chip.  results (may be NULL) is
+ * [n_events x result_count] uint8 meas_result_t for instances result_first.. (row-major by instance:
+ * results[(b-result_first)*n_events + e]). */
+int viekf_batch_run_tape(viekf_batch* h, const viekf_tape* tape, uint8_t* results, int64_t result_first,
+                         int64_t result_count);
+
+/* Upload a tape once (events, ids, per-instance values) and run it later without host<->device traffic. */
+typedef struct viekf_dev_tape viekf_dev_tape;
+int viekf_batch_upload_tape(viekf_batch* h, const viekf_tape* tape, viekf_dev_tape** out);
+void viekf_batch_free_tape(viekf_batch* h, viekf_dev_tape* t);
+/* n_first..n_first+n_run events; returns after enqueueing when async != 0 (viekf_batch_sync to wait). */
+int viekf_batch_run_dev_tape(viekf_batch* h, const viekf_dev_tape* t, int64_t ev_first, int64_t ev_count, int32_t async);
+int viekf_batch_sync(viekf_batch* h);
+/* cudaStream_t the handle launches on, as void* (for CUDA-event timing by the caller). */
+void* viekf_batch_stream(viekf_batch* h);
+/* Kernel launches issued by this handle so far. */
+int64_t viekf_batch_launch_count(const viekf_batch* h);
+
+/* Statistics: n_buckets x VIEKF_STAT_WIDTH doubles.  dev_ptr variant exposes the device buffer so the caller can
+ * all-reduce it in place with NCCL before reading it. */
+int viekf_batch_stats_reset(viekf_batch* h, int32_t n_buckets);
+int viekf_batch_stats(viekf_batch* h, double* out, int32_t n_buckets);
+void* viekf_batch_stats_dev_ptr(viekf_batch* h);
+
+/* Reset every instance to the configuration's initial state (re-run benchmarks without re-creating). */
+int viekf_batch_reset(viekf_batch* h);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

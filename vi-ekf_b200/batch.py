@@ -1,0 +1,182 @@
+"""BatchVIEKF: B reference-shaped filters behind the C ABI (include/viekf_batch.h).
+
+Method names, argument meaning and result codes follow the reference's vi_ekf::VIEKF
+(reference include/vi_ekf.h:243-337); every call acts on all B instances.
+"""
+import ctypes as C
+
+import numpy as np
+
+from . import abi
+
+
+def _p(a):
+    return a.ctypes.data_as(C.c_void_p) if a is not None else None
+
+
+class ViekfError(RuntimeError):
+    pass
+
+
+class BatchVIEKF:
+    def __init__(self, cfg=None, B=1, N=12, device=0):
+        self.L = abi.load_library()
+        self.cfg = cfg if cfg is not None else abi.default_config()
+        self.B, self.N = int(B), int(N)
+        self.MAX_X, self.MAX_DX = abi.max_x(N), abi.max_dx(N)
+        h = C.c_void_p()
+        self._chk(self.L.viekf_batch_create(C.byref(self.cfg), self.B, self.N, int(device), C.byref(h)))
+        self.h = h
+
+    def _chk(self, rc):
+        if rc != 0:
+            raise ViekfError(f"viekf_b200 error {rc}: {self.L.viekf_last_error().decode()}")
+
+    def close(self):
+        if getattr(self, "h", None):
+            self.L.viekf_batch_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    # ---- state access (reference vi_ekf.cpp:157-206) -------------------------------------------------
+    def set_x0(self, x0):
+        x0 = np.ascontiguousarray(x0, dtype=np.float64)
+        if x0.ndim == 1:
+            assert x0.size == 17
+            self._chk(self.L.viekf_batch_set_x0(self.h, _p(x0), 1))
+        else:
+            assert x0.shape == (self.B, 17)
+            self._chk(self.L.viekf_batch_set_x0(self.h, _p(x0), 0))
+
+    def perturb_x0(self, seed):
+        self._chk(self.L.viekf_batch_perturb_x0(self.h, C.c_uint64(seed)))
+
+    def get_state(self, first=0, count=None):
+        count = self.B - first if count is None else count
+        x = np.zeros((count, self.MAX_X))
+        self._chk(self.L.viekf_batch_get_state(self.h, first, count, _p(x)))
+        return x
+
+    def get_covariance(self, first=0, count=None):
+        count = self.B - first if count is None else count
+        P = np.zeros((count, self.MAX_DX, self.MAX_DX))
+        self._chk(self.L.viekf_batch_get_covariance(self.h, first, count, _p(P)))
+        return P.transpose(0, 2, 1)  # column-major per instance -> P[b, i, j]
+
+    def get_features(self, first=0, count=None):
+        count = self.B - first if count is None else count
+        ln = np.zeros(count, dtype=np.int32)
+        ids = np.full((count, max(self.N, 1)), -1, dtype=np.int32)
+        self._chk(self.L.viekf_batch_get_features(self.h, first, count, _p(ln), _p(ids)))
+        return ln, ids[:, : self.N]
+
+    def get_flags(self, first=0, count=None):
+        count = self.B - first if count is None else count
+        fl = np.zeros(count, dtype=np.uint32)
+        ctr = np.zeros((count, 3), dtype=np.uint32)
+        self._chk(self.L.viekf_batch_get_flags(self.h, first, count, _p(fl), _p(ctr)))
+        return fl, ctr
+
+    def get_time(self, first=0, count=None):
+        count = self.B - first if count is None else count
+        t = np.zeros(count)
+        self._chk(self.L.viekf_batch_get_time(self.h, first, count, _p(t)))
+        return t
+
+    # ---- per-call path (one launch per reference call) -----------------------------------------------
+    def propagate_state(self, u, t):
+        u = np.ascontiguousarray(u, dtype=np.float64)
+        bc = 1 if u.ndim == 1 else 0
+        assert u.shape[-1] == 6 and (bc or u.shape[0] == self.B)
+        self._chk(self.L.viekf_batch_propagate(self.h, _p(u), bc, float(t)))
+
+    def update(self, mtype, z, R, active=True, id=-1, depth=float("nan")):
+        z = np.ascontiguousarray(z, dtype=np.float64)
+        R = np.asfortranarray(np.atleast_2d(np.asarray(R, dtype=np.float64)))
+        bc = 1 if z.ndim == 1 else 0
+        zdim = z.shape[-1]
+        res = np.zeros(self.B, dtype=np.uint8)
+        self._chk(self.L.viekf_batch_update(self.h, int(mtype), _p(z), zdim, bc, _p(R), R.shape[0], int(active), int(id),
+                                            float(depth), _p(res)))
+        return res
+
+    def init_feature(self, pixel, id, depth=-1.0):
+        pixel = np.ascontiguousarray(pixel, dtype=np.float64)
+        bc = 1 if pixel.ndim == 1 else 0
+        ok = np.zeros(self.B, dtype=np.uint8)
+        self._chk(self.L.viekf_batch_init_feature(self.h, _p(pixel), bc, int(id), float(depth), _p(ok)))
+        return ok.astype(bool)
+
+    def clear_feature(self, id):
+        self._chk(self.L.viekf_batch_clear_feature(self.h, int(id)))
+
+    def keep_only_features(self, ids):
+        a = np.ascontiguousarray(ids, dtype=np.int32)
+        self._chk(self.L.viekf_batch_keep_only_features(self.h, _p(a), a.size))
+
+    def keyframe_reset(self):
+        self._chk(self.L.viekf_batch_keyframe_reset(self.h))
+
+    # ---- fused path -----------------------------------------------------------------------------------
+    def _mk_tape(self, events, id_pool, values):
+        events = np.ascontiguousarray(events, dtype=abi.EVENT_DTYPE)
+        idp = np.ascontiguousarray(id_pool if id_pool is not None else [0], dtype=np.int32)
+        t = abi.Tape()
+        t.events = events.ctypes.data
+        t.n_events = len(events)
+        t.id_pool = idp.ctypes.data
+        t.n_ids = idp.size
+        keep = [events, idp]
+        if values is not None:
+            values = np.ascontiguousarray(values, dtype=np.float64)
+            assert values.ndim == 2 and values.shape[0] == self.B
+            t.values = values.ctypes.data
+            t.values_stride = values.shape[1]
+            keep.append(values)
+        return t, keep
+
+    def run_tape(self, events, id_pool=None, values=None, results_first=0, results_count=0):
+        t, keep = self._mk_tape(events, id_pool, values)
+        res = np.zeros((results_count, len(events)), dtype=np.uint8) if results_count else None
+        self._chk(self.L.viekf_batch_run_tape(self.h, C.byref(t), _p(res), results_first, results_count))
+        return res
+
+    def upload_tape(self, events, id_pool=None, values=None):
+        t, keep = self._mk_tape(events, id_pool, values)
+        d = C.c_void_p()
+        self._chk(self.L.viekf_batch_upload_tape(self.h, C.byref(t), C.byref(d)))
+        return d
+
+    def free_tape(self, d):
+        self.L.viekf_batch_free_tape(self.h, d)
+
+    def run_dev_tape(self, d, first=0, count=-1, sync=True):
+        self._chk(self.L.viekf_batch_run_dev_tape(self.h, d, first, count, 0 if sync else 1))
+
+    def sync(self):
+        self._chk(self.L.viekf_batch_sync(self.h))
+
+    def stream(self):
+        return self.L.viekf_batch_stream(self.h)
+
+    def launch_count(self):
+        return self.L.viekf_batch_launch_count(self.h)
+
+    def stats_reset(self, n_buckets):
+        self._chk(self.L.viekf_batch_stats_reset(self.h, n_buckets))
+
+    def stats(self, n_buckets):
+        out = np.zeros((n_buckets, abi.STAT_WIDTH))
+        self._chk(self.L.viekf_batch_stats(self.h, _p(out), n_buckets))
+        return out
+
+    def stats_dev_ptr(self):
+        return self.L.viekf_batch_stats_dev_ptr(self.h)
+
+    def reset(self):
+        self._chk(self.L.viekf_batch_reset(self.h))
