@@ -113,6 +113,8 @@ typedef struct viekf_event {
   double z[8];    /* PROP: u = [acc(3), gyro(3)] in the IMU frame; UPD: z[0..zdim), z[4] = depth (FEAT);
                      INIT: pixel(2), z[4] = depth (NaN = unknown); STAT: true pos(3) vel(3) att(4)=10 -> see truth block */
   double R[9];    /* UPD: rdim x rdim column-major */
+  double sigma[8]; /* per-instance white noise added to z[k] (PROP: k<6, UPD: k<zdim, INIT: k<2) when the tape has a
+                      seed: z[k] += sigma[k] * N(0,1)(seed, instance, event index, k)   (include/viekf_noise.h) */
 } viekf_event;
 
 /* A tape is shared by all B instances (same control flow, Monte-Carlo use).  Per-instance values, when
@@ -125,6 +127,10 @@ typedef struct viekf_tape {
   int64_t n_ids;
   const double* values; /* host pointer, may be NULL */
   int64_t values_stride; /* doubles per instance */
+  uint64_t seed;         /* 0 = no generated noise; else Philox key for sigma / imu_bias_range (viekf_noise.h) */
+  double imu_bias_range[6]; /* PROP: u[k] += imu_bias_range[k] * U(-1,1)(seed, instance, k), constant per instance
+                               (multirotor_sim draws its IMU biases the same way, lib/multirotor_sim/src/simulator.cpp:140-160);
+                               STAT events add the same bias (rotated by q_b_u) to the true b_a / b_g */
 } viekf_tape;
 
 /* Statistics accumulated by STAT events, per bucket (all sums over the filters of this handle):
@@ -156,6 +162,9 @@ int viekf_batch_get_covariance(viekf_batch* h, int64_t first, int64_t count, dou
 int viekf_batch_get_features(viekf_batch* h, int64_t first, int64_t count, int32_t* len, int32_t* ids);
 /* sticky VIEKF_FLAG_* per filter, counters[3 x count] = {#gated, #fix_depth, #nan_gain}. */
 int viekf_batch_get_flags(viekf_batch* h, int64_t first, int64_t count, uint32_t* flags, uint32_t* counters);
+/* get_global_pose / global_pose_cov_ bookkeeping of keyframe_reset (vi_ekf_kfr.cpp:14-55): node pose [t(3), q(4)] x count
+ * and the accumulated 6x6 global covariance (column-major, may be NULL). */
+int viekf_batch_get_global_pose(viekf_batch* h, int64_t first, int64_t count, double* node_t3q4, double* gcov36);
 /* current filter time t_[i_] of each instance */
 int viekf_batch_get_time(viekf_batch* h, int64_t first, int64_t count, double* t);
 
@@ -204,6 +213,14 @@ void* viekf_batch_stats_dev_ptr(viekf_batch* h);
 
 /* Reset every instance to the configuration's initial state (re-run benchmarks without re-creating). */
 int viekf_batch_reset(viekf_batch* h);
+
+/* Global id of this handle's instance 0 (default 0).  Generated noise is keyed by the global instance id, so a batch
+ * sharded over several handles / GPUs draws exactly the streams the unsharded batch would. */
+int viekf_batch_set_instance_offset(viekf_batch* h, int64_t first_global_instance);
+
+/* FP64 FMA throughput probe (TFLOP/s, 2 flop per DFMA) of the handle's device: the roofline denominator of the
+ * compute-bound kernels (MEASURED_PEAKS.json carries no FP64 figure). */
+int viekf_fp64_peak_probe(int32_t device, double* tflops);
 
 #ifdef __cplusplus
 }

@@ -173,17 +173,24 @@ class OracleVIEKF:
         self.L.vo_global_pose(self.h, _p(t), _p(cov))
         return t, cov
 
-    def run_tape(self, events, id_pool=None, values=None, n_buckets=0):
+    def run_tape(self, events, id_pool=None, values=None, n_buckets=0, seed=0, bias_range=None, ginst=0, ev_first=0, ev_count=None):
         events = np.ascontiguousarray(events)
-        res = np.zeros(len(events), dtype=np.uint8)
+        res = np.full(len(events), 255, dtype=np.uint8)
         stats = np.zeros((max(n_buckets, 1), 40))
         idp = np.ascontiguousarray(id_pool, dtype=np.int32) if id_pool is not None else None
         vals = np.ascontiguousarray(values, dtype=np.float64) if values is not None else None
-        self.L.vo_run_tape(self.h, _p(events), C.c_int64(len(events)), _p(idp), _p(vals), _p(res), _p(stats), C.c_int(n_buckets))
+        br = np.ascontiguousarray(bias_range if bias_range is not None else np.zeros(6), dtype=np.float64)
+        n = len(events) - ev_first if ev_count is None else ev_count
+        self.L.vo_run_tape(self.h, _p(events), C.c_int64(n), _p(idp), _p(vals), _p(res), _p(stats), C.c_int(n_buckets),
+                           C.c_uint64(seed), _p(br), C.c_uint64(ginst), C.c_int64(ev_first))
         return res, stats[:n_buckets]
 
+    def perturb_x0(self, seed, ginst=0):
+        self.L.vo_perturb_x0(self.h, C.c_uint64(seed), C.c_uint64(ginst))
 
-def run_batch(cfg, NF, events, id_pool=None, values=None, x0=None, count=1, nthreads=1, want_P=True, n_buckets=0):
+
+def run_batch(cfg, NF, events, id_pool=None, values=None, x0=None, count=1, nthreads=1, want_P=True, n_buckets=0, seed=0,
+              bias_range=None, inst_off=0, perturb_seed=0, want_results=True):
     """`count` instances of one tape on `nthreads` host threads; returns dict with wall seconds and final x/P/..."""
     L = lib()
     events = np.ascontiguousarray(events)
@@ -198,15 +205,17 @@ def run_batch(cfg, NF, events, id_pool=None, values=None, x0=None, count=1, nthr
     x0a = np.ascontiguousarray(x0, dtype=np.float64) if x0 is not None else None
     x = np.zeros((count, MAX_X))
     P = np.zeros((count, MAX_DX, MAX_DX)) if want_P else None
-    res = np.zeros((count, len(events)), dtype=np.uint8)
+    res = np.zeros((count, len(events)), dtype=np.uint8) if want_results else None
     stats = np.zeros((max(n_buckets, 1), 40))
+    br = np.ascontiguousarray(bias_range if bias_range is not None else np.zeros(6), dtype=np.float64)
     lens = np.zeros(count, dtype=np.int32)
     ids = np.zeros((count, max(NF, 1)), dtype=np.int32)
     flags = np.zeros((count, 4), dtype=np.uint32)
     margins = np.zeros((count, 2))
     secs = L.vo_run_batch(C.byref(cfg), C.c_int(NF), _p(events), C.c_int64(len(events)), _p(idp), _p(vals), C.c_int64(stride),
                           _p(x0a), C.c_int64(count), C.c_int(nthreads), _p(x), _p(P), _p(res), _p(stats), C.c_int(n_buckets),
-                          _p(lens), _p(ids) if NF > 0 else None, _p(flags), _p(margins))
+                          _p(lens), _p(ids) if NF > 0 else None, _p(flags), _p(margins), C.c_uint64(seed), _p(br), C.c_int64(inst_off),
+                          C.c_uint64(perturb_seed))
     if P is not None:
         P = P.transpose(0, 2, 1)  # column-major per instance -> P[b, i, j]
     return dict(secs=secs, x=x, P=P, results=res, stats=stats[:n_buckets], len=lens, ids=ids[:, :NF], flags=flags, margins=margins)

@@ -111,9 +111,10 @@ void vo_global_pose(void* h, double* t3q4, double* cov36) {
   f->get_global_cov(cov36);
 }
 void vo_run_tape(void* h, const viekf_event* ev, int64_t n, const int32_t* id_pool, const double* values, uint8_t* results,
-                 double* stats, int n_buckets) {
-  ((VIEKF*)h)->run_tape(ev, n, id_pool, values, results, stats, n_buckets);
+                 double* stats, int n_buckets, uint64_t seed, const double* bias_range, uint64_t ginst, int64_t ev_first) {
+  ((VIEKF*)h)->run_tape(ev, n, id_pool, values, results, stats, n_buckets, seed, bias_range, ginst, ev_first);
 }
+void vo_perturb_x0(void* h, uint64_t seed, uint64_t ginst) { ((VIEKF*)h)->perturb_x0(seed, ginst); }
 
 // CPU baseline: `count` instances of the same tape, one instance per thread at a time over `nthreads` host
 // threads.  Returns wall seconds.  x_out ([MAX_X x count]) / P_out ([MAX_DX^2 x count]) / results_out /
@@ -121,7 +122,8 @@ void vo_run_tape(void* h, const viekf_event* ev, int64_t n, const int32_t* id_po
 double vo_run_batch(const viekf_config* cfg, int NF, const viekf_event* ev, int64_t n_ev, const int32_t* id_pool,
                     const double* values, int64_t values_stride, const double* x0 /*[17 x count] or null*/, int64_t count,
                     int nthreads, double* x_out, double* P_out, uint8_t* results_out, double* stats, int n_buckets,
-                    int* len_out, int* ids_out, unsigned* flags_out, double* margins_out) {
+                    int* len_out, int* ids_out, unsigned* flags_out, double* margins_out, uint64_t seed, const double* bias_range,
+                    int64_t inst_off, uint64_t perturb_seed) {
   std::atomic<int64_t> next(0);
   std::vector<std::vector<double>> tstats(nthreads, std::vector<double>((size_t)std::max(n_buckets, 0) * VIEKF_STAT_WIDTH, 0.0));
   auto t0 = std::chrono::steady_clock::now();
@@ -131,8 +133,9 @@ double vo_run_batch(const viekf_config* cfg, int NF, const viekf_event* ev, int6
       if (b >= count) break;
       VIEKF f(*cfg, NF, 2);
       if (x0) f.set_x0(x0 + 17 * b);
+      if (perturb_seed) f.perturb_x0(perturb_seed, (uint64_t)(inst_off + b));
       f.run_tape(ev, n_ev, id_pool, values ? values + b * values_stride : nullptr, results_out ? results_out + b * n_ev : nullptr,
-                 n_buckets > 0 ? tstats[tid].data() : nullptr, n_buckets);
+                 n_buckets > 0 ? tstats[tid].data() : nullptr, n_buckets, seed, bias_range, (uint64_t)(inst_off + b), 0);
       if (x_out) std::memcpy(x_out + (size_t)b * f.MAX_X, f.get_state().data(), sizeof(double) * f.MAX_X);
       if (P_out) std::memcpy(P_out + (size_t)b * f.MAX_DX * f.MAX_DX, f.get_covariance().d.data(), sizeof(double) * f.MAX_DX * f.MAX_DX);
       if (len_out) len_out[b] = f.get_len_features();

@@ -1,5 +1,6 @@
 // viekf_oracle.cpp -- TEST INFRASTRUCTURE (see header).  Dense restatement of reference src/vi_ekf/*.cpp.
 #include "viekf_oracle.hpp"
+#include "../include/viekf_noise.h"
 #include <array>
 #include <cstdio>
 
@@ -861,6 +862,10 @@ int VIEKF::update_direct(int type, const double* z, int zdim, const double* R, i
     init_feature(z, id, depth);
     return VIEKF_MEAS_NEW_FEATURE;
   }
+  // A feature-indexed model with an untracked id makes the reference index the state with -1 (UB,
+  // vi_ekf_meas.cpp:337,356,371,381); the tape semantics define it as MEAS_INVALID with no state change.
+  if ((type == VIEKF_FEAT || type == VIEKF_QZETA || type == VIEKF_DEPTH || type == VIEKF_INV_DEPTH) && global_to_local_feature_id(id) < 0)
+    return VIEKF_MEAS_INVALID;
   Meas m;
   std::memset(&m, 0, sizeof(m));
   m.t = t_[i_];
@@ -876,11 +881,46 @@ int VIEKF::update_direct(int type, const double* z, int zdim, const double* R, i
   return update(m);
 }
 
+void VIEKF::perturb_x0(uint64_t seed, uint64_t ginst) {
+  std::vector<double> d(MAX_DX, 0.0), out(MAX_X, 0.0);
+  for (int k = 0; k < 8; k++) {
+    double nn[2];
+    viekf_normal_pair(seed, ginst, VIEKF_NOISE_EVENT_X0, k, nn);
+    d[2 * k] = std::sqrt(cfg_.P0[2 * k]) * nn[0];
+    d[2 * k + 1] = std::sqrt(cfg_.P0[2 * k + 1]) * nn[1];
+  }
+  const int keep = len_features_;
+  len_features_ = 0;
+  out = x_[i_];
+  boxplus(x_[i_], d, out);
+  len_features_ = keep;
+  x_[i_] = out;
+}
+
 void VIEKF::run_tape(const viekf_event* ev, int64_t n, const int32_t* id_pool, const double* values, uint8_t* results,
-                     double* stats, int n_buckets) {
-  for (int64_t e = 0; e < n; e++) {
+                     double* stats, int n_buckets, uint64_t seed, const double* bias_range, uint64_t ginst, int64_t ev_first) {
+  double bias[6] = {0, 0, 0, 0, 0, 0};
+  if (seed && bias_range)
+    for (int k = 0; k < 6; k++) bias[k] = bias_range[k] * viekf_uniform_pm1(seed, ginst, VIEKF_NOISE_EVENT_BIAS, k);
+  for (int64_t e = ev_first; e < ev_first + n; e++) {
     const viekf_event& E = ev[e];
-    const double* zv = (E.noise >= 0 && values) ? values + 8 * (int64_t)E.noise : E.z;
+    const double* zsrc = (E.noise >= 0 && values) ? values + 8 * (int64_t)E.noise : E.z;
+    // per-instance value resolution (include/viekf_batch.h: viekf_event.sigma, viekf_tape.seed / imu_bias_range)
+    double zbuf[8];
+    for (int k = 0; k < 8; k++) zbuf[k] = zsrc[k];
+    if (seed && (E.kind == VIEKF_EV_PROP || E.kind == VIEKF_EV_UPD || E.kind == VIEKF_EV_INIT)) {
+      for (int k = 0; k < 8; k += 2)
+        if (E.sigma[k] != 0.0 || E.sigma[k + 1] != 0.0) {
+          double nn[2];
+          viekf_normal_pair(seed, ginst, (uint32_t)e, (uint32_t)(k >> 1), nn);
+          zbuf[k] += E.sigma[k] * nn[0];
+          zbuf[k + 1] += E.sigma[k + 1] * nn[1];
+        }
+      if (E.kind == VIEKF_EV_PROP)
+        for (int k = 0; k < 6; k++)
+          if (bias_range && bias_range[k] != 0.0) zbuf[k] += bias[k];
+    }
+    const double* zv = zbuf;
     int res = VIEKF_MEAS_NONE;
     switch (E.kind) {
       case VIEKF_EV_PROP:
@@ -913,6 +953,13 @@ void VIEKF::run_tape(const viekf_event* ev, int64_t n, const int32_t* id_pool, c
         for (int i = 0; i < 9; i++) xt[8 + i] = E.R[i];
         if (E.noise >= 0 && values)
           for (int i = 0; i < 6; i++) xt[xB_A + i] = zv[i];
+        if (seed) {  // the instance's generated IMU bias, in the body frame
+          V3 ba = q_b_u_.rota(v3(bias[0], bias[1], bias[2])), bg = q_b_u_.rota(v3(bias[3], bias[4], bias[5]));
+          for (int i = 0; i < 3; i++) {
+            xt[xB_A + i] += ba[i];
+            xt[xB_G + i] += bg[i];
+          }
+        }
         const std::vector<double>& x = x_[i_];
         double er[16];
         for (int i = 0; i < 6; i++) er[i] = xt[i] - x[i];

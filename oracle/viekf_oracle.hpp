@@ -316,8 +316,11 @@ class VIEKF {
 
   // In-order tape execution (semantics of include/viekf_batch.h).  values = this instance's value stream.
   // results[e] receives meas_result_t or VIEKF_MEAS_NONE.  stats may be null.
+  // seed / bias_range / ginst: generated per-instance noise (include/viekf_noise.h); ev_first: absolute index of ev[0]'s
+  // successor range [ev_first, ev_first + n) inside the tape (noise is keyed by the absolute event index).
   void run_tape(const viekf_event* ev, int64_t n, const int32_t* id_pool, const double* values, uint8_t* results, double* stats,
-                int n_buckets);
+                int n_buckets, uint64_t seed = 0, const double* bias_range = nullptr, uint64_t ginst = 0, int64_t ev_first = 0);
+  void perturb_x0(uint64_t seed, uint64_t ginst);  // x <- x [+] sqrt(P0) o n   (viekf_batch_perturb_x0)
   int update_direct(int type, const double* z, int zdim, const double* R, int rdim, bool active, int id, double depth);
 
   // workspace, public so that the ported jac_test properties can read them (the reference's dynamics()

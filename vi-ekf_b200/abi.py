@@ -69,18 +69,18 @@ def default_config():
     return c
 
 
-# numpy mirror of viekf_event (184 bytes)
+# numpy mirror of viekf_event (248 bytes)
 EVENT_DTYPE = np.dtype([
     ("kind", "<i4"), ("type", "<i4"), ("id", "<i4"), ("active", "<i4"), ("zdim", "<i4"), ("rdim", "<i4"),
     ("n_ids", "<i4"), ("ids_off", "<i4"), ("noise", "<i4"), ("pad", "<i4"),
-    ("t", "<f8"), ("z", "<f8", (8,)), ("R", "<f8", (9,)),
+    ("t", "<f8"), ("z", "<f8", (8,)), ("R", "<f8", (9,)), ("sigma", "<f8", (8,)),
 ], align=True)
-assert EVENT_DTYPE.itemsize == 184
+assert EVENT_DTYPE.itemsize == 248
 
 
 class Tape(C.Structure):
     _fields_ = [("events", C.c_void_p), ("n_events", C.c_int64), ("id_pool", C.c_void_p), ("n_ids", C.c_int64),
-                ("values", C.c_void_p), ("values_stride", C.c_int64)]
+                ("values", C.c_void_p), ("values_stride", C.c_int64), ("seed", C.c_uint64), ("imu_bias_range", C.c_double * 6)]
 
 
 def lib_path():
@@ -114,6 +114,9 @@ def load_library():
         "viekf_batch_get_features": (i32, [vp, i64, i64, vp, vp]),
         "viekf_batch_get_flags": (i32, [vp, i64, i64, vp, vp]),
         "viekf_batch_get_time": (i32, [vp, i64, i64, vp]),
+        "viekf_batch_get_global_pose": (i32, [vp, i64, i64, vp, vp]),
+        "viekf_batch_set_instance_offset": (i32, [vp, i64]),
+        "viekf_fp64_peak_probe": (i32, [i32, pd]),
         "viekf_batch_propagate": (i32, [vp, vp, i32, dbl]),
         "viekf_batch_update": (i32, [vp, i32, vp, i32, i32, vp, i32, i32, i32, dbl, vp]),
         "viekf_batch_init_feature": (i32, [vp, vp, i32, i32, dbl, vp]),

@@ -82,6 +82,16 @@ class BatchVIEKF:
         self._chk(self.L.viekf_batch_get_flags(self.h, first, count, _p(fl), _p(ctr)))
         return fl, ctr
 
+    def get_global_pose(self, first=0, count=None):
+        count = self.B - first if count is None else count
+        pose = np.zeros((count, 7))
+        cov = np.zeros((count, 6, 6))
+        self._chk(self.L.viekf_batch_get_global_pose(self.h, first, count, _p(pose), _p(cov)))
+        return pose, cov.transpose(0, 2, 1)
+
+    def set_instance_offset(self, first_global_instance):
+        self._chk(self.L.viekf_batch_set_instance_offset(self.h, int(first_global_instance)))
+
     def get_time(self, first=0, count=None):
         count = self.B - first if count is None else count
         t = np.zeros(count)
@@ -123,7 +133,7 @@ class BatchVIEKF:
         self._chk(self.L.viekf_batch_keyframe_reset(self.h))
 
     # ---- fused path -----------------------------------------------------------------------------------
-    def _mk_tape(self, events, id_pool, values):
+    def _mk_tape(self, events, id_pool, values, seed=0, bias_range=None):
         events = np.ascontiguousarray(events, dtype=abi.EVENT_DTYPE)
         idp = np.ascontiguousarray(id_pool if id_pool is not None else [0], dtype=np.int32)
         t = abi.Tape()
@@ -131,6 +141,9 @@ class BatchVIEKF:
         t.n_events = len(events)
         t.id_pool = idp.ctypes.data
         t.n_ids = idp.size
+        t.seed = int(seed)
+        if bias_range is not None:
+            t.imu_bias_range[:] = [float(v) for v in bias_range]
         keep = [events, idp]
         if values is not None:
             values = np.ascontiguousarray(values, dtype=np.float64)
@@ -140,14 +153,15 @@ class BatchVIEKF:
             keep.append(values)
         return t, keep
 
-    def run_tape(self, events, id_pool=None, values=None, results_first=0, results_count=0):
-        t, keep = self._mk_tape(events, id_pool, values)
+    def run_tape(self, events, id_pool=None, values=None, results_first=0, results_count=0, seed=0, bias_range=None):
+        """Whole tape through the C ABI with HOST buffers: upload, one fused launch, results back."""
+        t, keep = self._mk_tape(events, id_pool, values, seed, bias_range)
         res = np.zeros((results_count, len(events)), dtype=np.uint8) if results_count else None
         self._chk(self.L.viekf_batch_run_tape(self.h, C.byref(t), _p(res), results_first, results_count))
         return res
 
-    def upload_tape(self, events, id_pool=None, values=None):
-        t, keep = self._mk_tape(events, id_pool, values)
+    def upload_tape(self, events, id_pool=None, values=None, seed=0, bias_range=None):
+        t, keep = self._mk_tape(events, id_pool, values, seed, bias_range)
         d = C.c_void_p()
         self._chk(self.L.viekf_batch_upload_tape(self.h, C.byref(t), C.byref(d)))
         return d
@@ -180,3 +194,13 @@ class BatchVIEKF:
 
     def reset(self):
         self._chk(self.L.viekf_batch_reset(self.h))
+
+
+def fp64_peak_tflops(device=0):
+    """Measured FP64 FMA throughput of the device (the roofline denominator of the compute-bound kernels)."""
+    L = abi.load_library()
+    v = C.c_double(0.0)
+    rc = L.viekf_fp64_peak_probe(int(device), C.byref(v))
+    if rc != 0:
+        raise ViekfError(f"viekf_fp64_peak_probe: {rc}: {L.viekf_last_error().decode()}")
+    return v.value

@@ -1,0 +1,598 @@
+// viekf_capi.cu -- the C ABI of include/viekf_batch.h over the tape-executor kernels.
+//
+// Every entry point names the reference method it stands in for in include/viekf_batch.h.  There is no CPU
+// fallback: without a CUDA device viekf_batch_create fails with VIEKF_ERR_NODEVICE.
+#include <cuda_runtime.h>
+#include <math.h>
+#include <stdio.h>
+#include <stdlib.h>
+#include <string.h>
+#include <algorithm>
+#include <string>
+#include <vector>
+#include "viekf_engine.h"
+
+using vk::FilterMeta;
+using vk::KParams;
+
+static thread_local std::string g_err;
+
+struct viekf_dev_tape {
+  viekf_event* ev = nullptr;
+  int64_t n_events = 0;
+  int32_t* id_pool = nullptr;
+  double* values = nullptr;
+  int64_t vstride = 0;
+  uint64_t seed = 0;
+  double bias_range[6] = {0, 0, 0, 0, 0, 0};
+};
+
+struct viekf_batch {
+  viekf_config cfg;
+  int64_t B = 0;
+  int32_t N = 0;
+  int device = 0;
+  int sm_count = 0;
+  int group = 0;
+  cudaStream_t stream = nullptr;
+  KParams kp;
+  int64_t launches = 0;
+  // scratch for the per-call path
+  viekf_event* d_ev1 = nullptr;
+  double* d_vals = nullptr;   // [B][8]
+  int32_t* d_ids = nullptr;   // [KF_CAP]
+  uint8_t* d_res = nullptr;   // [B]
+  double* d_x0 = nullptr;     // [B][17]
+};
+
+static int fail(int code, const char* what, cudaError_t e = cudaSuccess) {
+  char buf[512];
+  if (e != cudaSuccess)
+    snprintf(buf, sizeof(buf), "%s: %s", what, cudaGetErrorString(e));
+  else
+    snprintf(buf, sizeof(buf), "%s", what);
+  g_err = buf;
+  return code;
+}
+#define CK(call)                                                    \
+  do {                                                              \
+    cudaError_t e__ = (call);                                       \
+    if (e__ != cudaSuccess) return fail(VIEKF_ERR_CUDA, #call, e__); \
+  } while (0)
+
+static void quat_R(const double* q, double* m) {
+  const double w = q[0], x = q[1], y = q[2], z = q[3];
+  const double wx = w * x, wy = w * y, wz = w * z, xx = x * x, xy = x * y, xz = x * z, yy = y * y, yz = y * z, zz = z * z;
+  m[0] = 1. - 2. * yy - 2. * zz; m[1] = 2. * xy + 2. * wz; m[2] = 2. * xz - 2. * wy;
+  m[3] = 2. * xy - 2. * wz; m[4] = 1. - 2. * xx - 2. * zz; m[5] = 2. * yz + 2. * wx;
+  m[6] = 2. * xz + 2. * wy; m[7] = 2. * yz - 2. * wx; m[8] = 1. - 2. * xx - 2. * yy;
+}
+
+static void fill_params(viekf_batch* h) {
+  KParams& p = h->kp;
+  const viekf_config& c = h->cfg;
+  memcpy(p.x0, c.x0, sizeof(p.x0));
+  memcpy(p.P0, c.P0, sizeof(p.P0));
+  memcpy(p.Qx, c.Qx, sizeof(p.Qx));
+  memcpy(p.lam, c.lambda, sizeof(p.lam));
+  memcpy(p.Qu, c.Qu, sizeof(p.Qu));
+  memcpy(p.P0f, c.P0_feat, sizeof(p.P0f));
+  memcpy(p.Qxf, c.Qx_feat, sizeof(p.Qxf));
+  memcpy(p.lamf, c.lambda_feat, sizeof(p.lamf));
+  memcpy(p.cc, c.cam_center, sizeof(p.cc));
+  memcpy(p.fl, c.focal_len, sizeof(p.fl));
+  memcpy(p.qbc, c.q_b_c, sizeof(p.qbc));
+  memcpy(p.pbc, c.p_b_c, sizeof(p.pbc));
+  memcpy(p.qbu, c.q_b_u, sizeof(p.qbu));
+  quat_R(c.q_b_c, p.Rbc);
+  const double* t = c.p_b_c;
+  const double sp[9] = {0, -t[2], t[1], t[2], 0, -t[0], -t[1], t[0], 0};
+  for (int i = 0; i < 3; i++)
+    for (int j = 0; j < 3; j++) {
+      double s = 0;
+      for (int k = 0; k < 3; k++) s += p.Rbc[i * 3 + k] * sp[k * 3 + j];
+      p.RbcSp[i * 3 + j] = s;
+    }
+  p.min_depth = c.min_depth;
+  p.kf_thresh = c.keyframe_overlap_threshold;
+  p.use_drag = c.use_drag_term;
+  p.use_partial = c.use_partial_update;
+  p.use_kfreset = c.use_keyframe_reset;
+}
+
+extern "C" {
+
+const char* viekf_last_error(void) { return g_err.c_str(); }
+
+void viekf_config_default(viekf_config* c) {
+  // reference params/ekf.yaml
+  memset(c, 0, sizeof(*c));
+  const double x0[17] = {0, 0, -2, 0, 0, 0, 1, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0.1};
+  memcpy(c->x0, x0, sizeof(x0));
+  for (int i = 0; i < 9; i++) c->P0[i] = 1e-3;
+  for (int i = 9; i < 12; i++) c->P0[i] = 2e-1;
+  for (int i = 12; i < 15; i++) c->P0[i] = 1e-1;
+  c->P0[15] = 1e-6;
+  for (int i = 0; i < 9; i++) c->lambda[i] = 1.0;
+  for (int i = 9; i < 15; i++) c->lambda[i] = 0.1;
+  c->lambda[15] = 0.01;
+  const double Qu[6] = {1.0, 1.0, 1.0, 4e-4, 4e-4, 4e-4};
+  memcpy(c->Qu, Qu, sizeof(Qu));
+  c->P0_feat[0] = 0.01; c->P0_feat[1] = 0.01; c->P0_feat[2] = 0.3;
+  c->lambda_feat[0] = 1.0; c->lambda_feat[1] = 1.0; c->lambda_feat[2] = 0.4;
+  c->cam_center[0] = 315.83184814453125; c->cam_center[1] = 242.1165771484375;
+  c->focal_len[0] = 611.1864013671875; c->focal_len[1] = 611.5557861328125;
+  const double qbc[4] = {0.9974335273839892, 0.019768487288642146, -0.03564306227555538, 0.05886541830542371};
+  memcpy(c->q_b_c, qbc, sizeof(qbc));
+  const double pbc[3] = {0.17363129, -0.02205945, 0.05490228};
+  memcpy(c->p_b_c, pbc, sizeof(pbc));
+  const double qbu[4] = {0.993760669165504, 0.0497294816014604, 0.0997086508721388, 0.00498959122946198};
+  memcpy(c->q_b_u, qbu, sizeof(qbu));
+  c->min_depth = 1.5;
+  c->keyframe_overlap_threshold = 0.8;
+  c->use_drag_term = 1;
+  c->use_partial_update = 1;
+  c->use_keyframe_reset = 1;
+}
+
+int viekf_batch_create(const viekf_config* cfg, int64_t B, int32_t N, int32_t device, viekf_batch** out) {
+  if (!cfg || !out || B <= 0 || N < 0 || N > 64) return fail(VIEKF_ERR_ARG, "viekf_batch_create: bad argument (need B>0, 0<=N<=64)");
+  int ndev = 0;
+  cudaError_t e = cudaGetDeviceCount(&ndev);
+  if (e != cudaSuccess || ndev <= 0) return fail(VIEKF_ERR_NODEVICE, "viekf_batch_create: no CUDA device (there is no CPU fallback)", e);
+  if (device < 0 || device >= ndev) return fail(VIEKF_ERR_ARG, "viekf_batch_create: bad device ordinal");
+  CK(cudaSetDevice(device));
+  cudaDeviceProp prop;
+  CK(cudaGetDeviceProperties(&prop, device));
+  viekf_batch* h = new viekf_batch();
+  h->cfg = *cfg;
+  h->B = B;
+  h->N = N;
+  h->device = device;
+  h->sm_count = prop.multiProcessorCount;
+  h->group = vk::group_size_for(N);
+  if (const char* g = getenv("VIEKF_GROUP")) {
+    const int v = atoi(g);
+    if (v == 32 || v == 64 || v == 128 || v == 256) h->group = v;
+  }
+  const size_t need = vk::smem_bytes_per_filter(N) * ((h->group >= 128 ? h->group : 128) / h->group);
+  if (need > (size_t)prop.sharedMemPerBlockOptin) {
+    delete h;
+    return fail(VIEKF_ERR_UNSUPPORTED, "viekf_batch_create: N too large for the shared-memory resident covariance");
+  }
+  memset(&h->kp, 0, sizeof(h->kp));
+  fill_params(h);
+  KParams& p = h->kp;
+  p.N = N;
+  p.B = B;
+  p.inst_off = 0;
+  const int nmax = 16 + 3 * N;
+  p.xs = (17 + 5 * N + 1) & ~1;
+  p.ps = (nmax * (nmax + 1) / 2 + 1) & ~1;
+  auto cleanup = [&](int code, const char* what, cudaError_t ce) {
+    viekf_batch_destroy(h);
+    return fail(code, what, ce);
+  };
+  if ((e = cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking)) != cudaSuccess) return cleanup(VIEKF_ERR_CUDA, "cudaStreamCreate", e);
+  if ((e = cudaMalloc(&p.x, sizeof(double) * p.xs * B)) != cudaSuccess) return cleanup(VIEKF_ERR_NOMEM, "cudaMalloc x", e);
+  if ((e = cudaMalloc(&p.P, sizeof(double) * p.ps * B)) != cudaSuccess) return cleanup(VIEKF_ERR_NOMEM, "cudaMalloc P", e);
+  if ((e = cudaMalloc(&p.meta, sizeof(FilterMeta) * B)) != cudaSuccess) return cleanup(VIEKF_ERR_NOMEM, "cudaMalloc meta", e);
+  if ((e = cudaMalloc(&p.ids, sizeof(int32_t) * (N > 0 ? N : 1) * B)) != cudaSuccess) return cleanup(VIEKF_ERR_NOMEM, "cudaMalloc ids", e);
+  if ((e = cudaMalloc(&p.kf_ids, sizeof(int32_t) * vk::KF_CAP * B)) != cudaSuccess) return cleanup(VIEKF_ERR_NOMEM, "cudaMalloc kf_ids", e);
+  if ((e = cudaMalloc(&h->d_ev1, sizeof(viekf_event))) != cudaSuccess) return cleanup(VIEKF_ERR_NOMEM, "cudaMalloc ev", e);
+  if ((e = cudaMalloc(&h->d_ids, sizeof(int32_t) * vk::KF_CAP)) != cudaSuccess) return cleanup(VIEKF_ERR_NOMEM, "cudaMalloc ids scratch", e);
+  if ((e = cudaMemsetAsync(p.x, 0, sizeof(double) * p.xs * B, h->stream)) != cudaSuccess) return cleanup(VIEKF_ERR_CUDA, "memset x", e);
+  if ((e = cudaMemsetAsync(p.ids, 0xff, sizeof(int32_t) * (N > 0 ? N : 1) * B, h->stream)) != cudaSuccess) return cleanup(VIEKF_ERR_CUDA, "memset ids", e);
+  if ((e = vk::launch_reset(p, h->stream)) != cudaSuccess) return cleanup(VIEKF_ERR_CUDA, "reset kernel", e);
+  if ((e = cudaStreamSynchronize(h->stream)) != cudaSuccess) return cleanup(VIEKF_ERR_CUDA, "reset sync", e);
+  h->launches = 0;
+  *out = h;
+  return VIEKF_OK;
+}
+
+void viekf_batch_destroy(viekf_batch* h) {
+  if (!h) return;
+  cudaSetDevice(h->device);
+  if (h->stream) cudaStreamSynchronize(h->stream);
+  cudaFree(h->kp.x);
+  cudaFree(h->kp.P);
+  cudaFree(h->kp.meta);
+  cudaFree(h->kp.ids);
+  cudaFree(h->kp.kf_ids);
+  cudaFree(h->kp.stats);
+  cudaFree(h->d_ev1);
+  cudaFree(h->d_vals);
+  cudaFree(h->d_ids);
+  cudaFree(h->d_res);
+  cudaFree(h->d_x0);
+  if (h->stream) cudaStreamDestroy(h->stream);
+  delete h;
+}
+
+int viekf_batch_reset(viekf_batch* h) {
+  if (!h) return fail(VIEKF_ERR_ARG, "null handle");
+  CK(cudaSetDevice(h->device));
+  CK(vk::launch_reset(h->kp, h->stream));
+  CK(cudaStreamSynchronize(h->stream));
+  return VIEKF_OK;
+}
+
+int viekf_batch_set_instance_offset(viekf_batch* h, int64_t first) {
+  if (!h || first < 0) return fail(VIEKF_ERR_ARG, "bad argument");
+  h->kp.inst_off = first;
+  return VIEKF_OK;
+}
+
+int viekf_batch_set_x0(viekf_batch* h, const double* x0, int32_t broadcast) {
+  if (!h || !x0) return fail(VIEKF_ERR_ARG, "bad argument");
+  CK(cudaSetDevice(h->device));
+  if (!h->d_x0) CK(cudaMalloc(&h->d_x0, sizeof(double) * 17 * h->B));
+  CK(cudaMemcpyAsync(h->d_x0, x0, sizeof(double) * 17 * (broadcast ? 1 : h->B), cudaMemcpyHostToDevice, h->stream));
+  CK(vk::launch_set_x0(h->kp, h->d_x0, broadcast, h->stream));
+  CK(cudaStreamSynchronize(h->stream));
+  return VIEKF_OK;
+}
+
+int viekf_batch_perturb_x0(viekf_batch* h, uint64_t seed) {
+  if (!h) return fail(VIEKF_ERR_ARG, "null handle");
+  CK(cudaSetDevice(h->device));
+  CK(vk::launch_perturb(h->kp, seed, h->stream));
+  CK(cudaStreamSynchronize(h->stream));
+  return VIEKF_OK;
+}
+
+static int check_range(viekf_batch* h, int64_t first, int64_t count, const void* ptr) {
+  if (!h || !ptr || first < 0 || count < 0 || first + count > h->B) return fail(VIEKF_ERR_ARG, "bad instance range or null pointer");
+  return VIEKF_OK;
+}
+
+int viekf_batch_get_state(viekf_batch* h, int64_t first, int64_t count, double* x) {
+  if (int rc = check_range(h, first, count, x)) return rc;
+  if (count == 0) return VIEKF_OK;
+  CK(cudaSetDevice(h->device));
+  const size_t bytes = sizeof(double) * (17 + 5 * h->N) * count;
+  double* d = nullptr;
+  CK(cudaMalloc(&d, bytes));
+  cudaError_t e = vk::launch_unpack_state(h->kp, first, count, d, h->stream);
+  if (e == cudaSuccess) e = cudaMemcpyAsync(x, d, bytes, cudaMemcpyDeviceToHost, h->stream);
+  if (e == cudaSuccess) e = cudaStreamSynchronize(h->stream);
+  cudaFree(d);
+  if (e != cudaSuccess) return fail(VIEKF_ERR_CUDA, "get_state", e);
+  return VIEKF_OK;
+}
+
+int viekf_batch_get_covariance(viekf_batch* h, int64_t first, int64_t count, double* P) {
+  if (int rc = check_range(h, first, count, P)) return rc;
+  if (count == 0) return VIEKF_OK;
+  CK(cudaSetDevice(h->device));
+  const int64_t n = 16 + 3 * h->N;
+  // unpack in slabs so a large batch never needs a full dense copy on the device
+  const int64_t slab = std::max<int64_t>(1, (int64_t)(256ll << 20) / (int64_t)(sizeof(double) * n * n));
+  double* d = nullptr;
+  CK(cudaMalloc(&d, sizeof(double) * n * n * std::min(slab, count)));
+  cudaError_t e = cudaSuccess;
+  for (int64_t o = 0; o < count && e == cudaSuccess; o += slab) {
+    const int64_t c = std::min(slab, count - o);
+    e = vk::launch_unpack_cov(h->kp, first + o, c, d, h->stream);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(P + o * n * n, d, sizeof(double) * n * n * c, cudaMemcpyDeviceToHost, h->stream);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(h->stream);
+  }
+  cudaFree(d);
+  if (e != cudaSuccess) return fail(VIEKF_ERR_CUDA, "get_covariance", e);
+  return VIEKF_OK;
+}
+
+static int fetch_meta(viekf_batch* h, int64_t first, int64_t count, std::vector<FilterMeta>& m) {
+  m.resize((size_t)count);
+  CK(cudaSetDevice(h->device));
+  CK(cudaStreamSynchronize(h->stream));
+  CK(cudaMemcpy(m.data(), h->kp.meta + first, sizeof(FilterMeta) * count, cudaMemcpyDeviceToHost));
+  return VIEKF_OK;
+}
+
+int viekf_batch_get_features(viekf_batch* h, int64_t first, int64_t count, int32_t* len, int32_t* ids) {
+  if (int rc = check_range(h, first, count, len)) return rc;
+  if (count == 0) return VIEKF_OK;
+  std::vector<FilterMeta> m;
+  if (int rc = fetch_meta(h, first, count, m)) return rc;
+  for (int64_t b = 0; b < count; b++) len[b] = m[b].len;
+  if (ids && h->N > 0) {
+    CK(cudaMemcpy(ids, h->kp.ids + first * h->N, sizeof(int32_t) * h->N * count, cudaMemcpyDeviceToHost));
+    for (int64_t b = 0; b < count; b++)
+      for (int i = len[b]; i < h->N; i++) ids[b * h->N + i] = -1;
+  }
+  return VIEKF_OK;
+}
+
+int viekf_batch_get_flags(viekf_batch* h, int64_t first, int64_t count, uint32_t* flags, uint32_t* counters) {
+  if (int rc = check_range(h, first, count, flags)) return rc;
+  if (count == 0) return VIEKF_OK;
+  std::vector<FilterMeta> m;
+  if (int rc = fetch_meta(h, first, count, m)) return rc;
+  for (int64_t b = 0; b < count; b++) {
+    flags[b] = m[b].flags;
+    if (counters) {
+      counters[3 * b] = m[b].n_gated;
+      counters[3 * b + 1] = m[b].n_fix;
+      counters[3 * b + 2] = m[b].n_nan_gain;
+    }
+  }
+  return VIEKF_OK;
+}
+
+int viekf_batch_get_time(viekf_batch* h, int64_t first, int64_t count, double* t) {
+  if (int rc = check_range(h, first, count, t)) return rc;
+  if (count == 0) return VIEKF_OK;
+  std::vector<FilterMeta> m;
+  if (int rc = fetch_meta(h, first, count, m)) return rc;
+  for (int64_t b = 0; b < count; b++) t[b] = m[b].t;
+  return VIEKF_OK;
+}
+
+int viekf_batch_get_global_pose(viekf_batch* h, int64_t first, int64_t count, double* node_t3q4, double* gcov36) {
+  if (int rc = check_range(h, first, count, node_t3q4)) return rc;
+  if (count == 0) return VIEKF_OK;
+  std::vector<FilterMeta> m;
+  if (int rc = fetch_meta(h, first, count, m)) return rc;
+  for (int64_t b = 0; b < count; b++) {
+    for (int i = 0; i < 3; i++) node_t3q4[7 * b + i] = m[b].node_t[i];
+    for (int i = 0; i < 4; i++) node_t3q4[7 * b + 3 + i] = m[b].node_q[i];
+    if (gcov36) memcpy(gcov36 + 36 * b, m[b].gcov, sizeof(double) * 36);
+  }
+  return VIEKF_OK;
+}
+
+// ---- launching --------------------------------------------------------------------------------------------------
+static int run_range(viekf_batch* h, const viekf_dev_tape* t, int64_t ev_first, int64_t ev_count, uint8_t* d_results, int64_t res_first,
+                     int64_t res_count) {
+  KParams p = h->kp;
+  p.ev = t->ev;
+  p.n_events = t->n_events;
+  p.ev_first = ev_first;
+  p.ev_count = ev_count;
+  p.id_pool = t->id_pool;
+  p.values = t->values;
+  p.vstride = t->vstride;
+  p.seed = t->seed;
+  memcpy(p.bias_range, t->bias_range, sizeof(p.bias_range));
+  p.results = d_results;
+  p.res_first = res_first;
+  p.res_count = res_count;
+  CK(vk::launch_tape(p, h->group, h->sm_count, h->stream));
+  h->launches++;
+  return VIEKF_OK;
+}
+
+static int run_single_event(viekf_batch* h, const viekf_event& ev, const double* host_vals, int vdim, int broadcast, uint8_t* host_res) {
+  CK(cudaSetDevice(h->device));
+  viekf_event e = ev;
+  viekf_dev_tape t;
+  t.ev = h->d_ev1;
+  t.n_events = 1;
+  t.id_pool = h->d_ids;
+  if (host_vals && !broadcast) {
+    if (!h->d_vals) CK(cudaMalloc(&h->d_vals, sizeof(double) * 8 * h->B));
+    CK(cudaMemcpyAsync(h->d_vals, host_vals, sizeof(double) * vdim * h->B, cudaMemcpyHostToDevice, h->stream));
+    t.values = h->d_vals;
+    t.vstride = vdim;
+    e.noise = 0;
+  } else {
+    if (host_vals)
+      for (int k = 0; k < vdim && k < 8; k++) e.z[k] = host_vals[k];
+    e.noise = -1;
+  }
+  CK(cudaMemcpyAsync(h->d_ev1, &e, sizeof(e), cudaMemcpyHostToDevice, h->stream));
+  uint8_t* dres = nullptr;
+  if (host_res) {
+    if (!h->d_res) CK(cudaMalloc(&h->d_res, h->B));
+    dres = h->d_res;
+  }
+  if (int rc = run_range(h, &t, 0, 1, dres, 0, dres ? h->B : 0)) return rc;
+  if (host_res) CK(cudaMemcpyAsync(host_res, dres, h->B, cudaMemcpyDeviceToHost, h->stream));
+  CK(cudaStreamSynchronize(h->stream));
+  return VIEKF_OK;
+}
+
+static viekf_event blank_event(int kind) {
+  viekf_event e;
+  memset(&e, 0, sizeof(e));
+  e.kind = kind;
+  e.id = -1;
+  e.noise = -1;
+  return e;
+}
+
+int viekf_batch_propagate(viekf_batch* h, const double* u, int32_t broadcast, double t) {
+  if (!h || !u) return fail(VIEKF_ERR_ARG, "bad argument");
+  viekf_event e = blank_event(VIEKF_EV_PROP);
+  e.t = t;
+  return run_single_event(h, e, u, 6, broadcast, nullptr);
+}
+
+int viekf_batch_update(viekf_batch* h, int32_t type, const double* z, int32_t zdim, int32_t broadcast, const double* R, int32_t rdim,
+                       int32_t active, int32_t id, double depth, uint8_t* result) {
+  if (!h || !z || !R || zdim < 1 || zdim > 4 || rdim < 1 || rdim > 3 || type < 0 || type >= VIEKF_TOTAL_MEAS)
+    return fail(VIEKF_ERR_ARG, "viekf_batch_update: bad argument");
+  viekf_event e = blank_event(VIEKF_EV_UPD);
+  e.type = type;
+  e.zdim = zdim;
+  e.rdim = rdim;
+  e.active = active;
+  e.id = id;
+  e.z[4] = depth;
+  for (int i = 0; i < rdim * rdim; i++) e.R[i] = R[i];
+  return run_single_event(h, e, z, zdim, broadcast, result);
+}
+
+int viekf_batch_init_feature(viekf_batch* h, const double* pixel, int32_t broadcast, int32_t id, double depth, uint8_t* ok) {
+  if (!h || !pixel) return fail(VIEKF_ERR_ARG, "bad argument");
+  viekf_event e = blank_event(VIEKF_EV_INIT);
+  e.id = id;
+  e.z[4] = depth;
+  return run_single_event(h, e, pixel, 2, broadcast, ok);
+}
+
+int viekf_batch_clear_feature(viekf_batch* h, int32_t id) {
+  if (!h) return fail(VIEKF_ERR_ARG, "null handle");
+  viekf_event e = blank_event(VIEKF_EV_CLEAR);
+  e.id = id;
+  return run_single_event(h, e, nullptr, 0, 1, nullptr);
+}
+
+int viekf_batch_keep_only_features(viekf_batch* h, const int32_t* ids, int32_t n) {
+  if (!h || n < 0 || (n > 0 && !ids)) return fail(VIEKF_ERR_ARG, "bad argument");
+  if (n > vk::KF_CAP) return fail(VIEKF_ERR_UNSUPPORTED, "keep_only_features: more than 64 ids");
+  CK(cudaSetDevice(h->device));
+  if (n > 0) CK(cudaMemcpyAsync(h->d_ids, ids, sizeof(int32_t) * n, cudaMemcpyHostToDevice, h->stream));
+  viekf_event e = blank_event(VIEKF_EV_KEEP);
+  e.n_ids = n;
+  e.ids_off = 0;
+  return run_single_event(h, e, nullptr, 0, 1, nullptr);
+}
+
+int viekf_batch_keyframe_reset(viekf_batch* h) {
+  if (!h) return fail(VIEKF_ERR_ARG, "null handle");
+  viekf_event e = blank_event(VIEKF_EV_KFRESET);
+  return run_single_event(h, e, nullptr, 0, 1, nullptr);
+}
+
+static int validate_tape(const viekf_tape* t) {
+  if (!t || t->n_events < 0 || (t->n_events > 0 && !t->events)) return fail(VIEKF_ERR_ARG, "tape: null events");
+  for (int64_t i = 0; i < t->n_events; i++) {
+    const viekf_event& e = t->events[i];
+    if (e.kind < 0 || e.kind > VIEKF_EV_KFRESET) return fail(VIEKF_ERR_ARG, "tape: unknown event kind");
+    if (e.kind == VIEKF_EV_UPD && (e.zdim < 1 || e.zdim > 4 || e.rdim < 1 || e.rdim > 3 || e.type < 0 || e.type >= VIEKF_TOTAL_MEAS))
+      return fail(VIEKF_ERR_ARG, "tape: bad UPD event");
+    if (e.kind == VIEKF_EV_KEEP) {
+      if (e.n_ids < 0 || e.ids_off < 0 || e.ids_off + e.n_ids > t->n_ids || (e.n_ids > 0 && !t->id_pool)) return fail(VIEKF_ERR_ARG, "tape: KEEP ids out of range");
+      if (e.n_ids > vk::KF_CAP) return fail(VIEKF_ERR_UNSUPPORTED, "tape: KEEP with more than 64 ids");
+    }
+    if (e.noise >= 0 && t->values && 8 * ((int64_t)e.noise + 1) > t->values_stride) return fail(VIEKF_ERR_ARG, "tape: value block beyond values_stride");
+  }
+  return VIEKF_OK;
+}
+
+int viekf_batch_upload_tape(viekf_batch* h, const viekf_tape* tape, viekf_dev_tape** out) {
+  if (!h || !out) return fail(VIEKF_ERR_ARG, "bad argument");
+  if (int rc = validate_tape(tape)) return rc;
+  CK(cudaSetDevice(h->device));
+  viekf_dev_tape* d = new viekf_dev_tape();
+  d->n_events = tape->n_events;
+  d->seed = tape->seed;
+  memcpy(d->bias_range, tape->imu_bias_range, sizeof(d->bias_range));
+  cudaError_t e = cudaSuccess;
+  if (tape->n_events > 0) {
+    e = cudaMalloc(&d->ev, sizeof(viekf_event) * tape->n_events);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(d->ev, tape->events, sizeof(viekf_event) * tape->n_events, cudaMemcpyHostToDevice, h->stream);
+  }
+  if (e == cudaSuccess && tape->n_ids > 0 && tape->id_pool) {
+    e = cudaMalloc(&d->id_pool, sizeof(int32_t) * tape->n_ids);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(d->id_pool, tape->id_pool, sizeof(int32_t) * tape->n_ids, cudaMemcpyHostToDevice, h->stream);
+  }
+  if (e == cudaSuccess && tape->values && tape->values_stride > 0) {
+    d->vstride = tape->values_stride;
+    e = cudaMalloc(&d->values, sizeof(double) * tape->values_stride * h->B);
+    if (e == cudaSuccess)
+      e = cudaMemcpyAsync(d->values, tape->values, sizeof(double) * tape->values_stride * h->B, cudaMemcpyHostToDevice, h->stream);
+  }
+  if (e == cudaSuccess) e = cudaStreamSynchronize(h->stream);
+  if (e != cudaSuccess) {
+    viekf_batch_free_tape(h, d);
+    return fail(e == cudaErrorMemoryAllocation ? VIEKF_ERR_NOMEM : VIEKF_ERR_CUDA, "upload_tape", e);
+  }
+  *out = d;
+  return VIEKF_OK;
+}
+
+void viekf_batch_free_tape(viekf_batch* h, viekf_dev_tape* t) {
+  if (!t) return;
+  if (h) {
+    cudaSetDevice(h->device);
+    cudaStreamSynchronize(h->stream);
+  }
+  cudaFree(t->ev);
+  cudaFree(t->id_pool);
+  cudaFree(t->values);
+  delete t;
+}
+
+int viekf_batch_run_dev_tape(viekf_batch* h, const viekf_dev_tape* t, int64_t ev_first, int64_t ev_count, int32_t async) {
+  if (!h || !t) return fail(VIEKF_ERR_ARG, "bad argument");
+  if (ev_count < 0) ev_count = t->n_events - ev_first;
+  if (ev_first < 0 || ev_first + ev_count > t->n_events) return fail(VIEKF_ERR_ARG, "event range out of the tape");
+  if (ev_count == 0) return VIEKF_OK;
+  CK(cudaSetDevice(h->device));
+  if (int rc = run_range(h, t, ev_first, ev_count, nullptr, 0, 0)) return rc;
+  if (!async) CK(cudaStreamSynchronize(h->stream));
+  return VIEKF_OK;
+}
+
+int viekf_batch_run_tape(viekf_batch* h, const viekf_tape* tape, uint8_t* results, int64_t result_first, int64_t result_count) {
+  if (!h) return fail(VIEKF_ERR_ARG, "null handle");
+  if (results && (result_first < 0 || result_count < 0 || result_first + result_count > h->B)) return fail(VIEKF_ERR_ARG, "bad result range");
+  viekf_dev_tape* d = nullptr;
+  if (int rc = viekf_batch_upload_tape(h, tape, &d)) return rc;
+  int rc = VIEKF_OK;
+  uint8_t* dres = nullptr;
+  cudaError_t e = cudaSuccess;
+  if (results && result_count > 0 && tape->n_events > 0) {
+    e = cudaMalloc(&dres, (size_t)result_count * tape->n_events);
+    if (e == cudaSuccess) e = cudaMemsetAsync(dres, 0xff, (size_t)result_count * tape->n_events, h->stream);
+  }
+  if (e == cudaSuccess && tape->n_events > 0) rc = run_range(h, d, 0, tape->n_events, dres, result_first, dres ? result_count : 0);
+  if (rc == VIEKF_OK && e == cudaSuccess && dres) e = cudaMemcpyAsync(results, dres, (size_t)result_count * tape->n_events, cudaMemcpyDeviceToHost, h->stream);
+  if (e == cudaSuccess) e = cudaStreamSynchronize(h->stream);
+  cudaFree(dres);
+  viekf_batch_free_tape(h, d);
+  if (rc != VIEKF_OK) return rc;
+  if (e != cudaSuccess) return fail(VIEKF_ERR_CUDA, "run_tape", e);
+  return VIEKF_OK;
+}
+
+int viekf_batch_sync(viekf_batch* h) {
+  if (!h) return fail(VIEKF_ERR_ARG, "null handle");
+  CK(cudaSetDevice(h->device));
+  CK(cudaStreamSynchronize(h->stream));
+  return VIEKF_OK;
+}
+
+void* viekf_batch_stream(viekf_batch* h) { return h ? (void*)h->stream : nullptr; }
+int64_t viekf_batch_launch_count(const viekf_batch* h) { return h ? h->launches : 0; }
+
+int viekf_batch_stats_reset(viekf_batch* h, int32_t n_buckets) {
+  if (!h || n_buckets < 0) return fail(VIEKF_ERR_ARG, "bad argument");
+  CK(cudaSetDevice(h->device));
+  CK(cudaStreamSynchronize(h->stream));
+  if (n_buckets != h->kp.n_buckets) {
+    cudaFree(h->kp.stats);
+    h->kp.stats = nullptr;
+    h->kp.n_buckets = 0;
+    if (n_buckets > 0) {
+      CK(cudaMalloc(&h->kp.stats, sizeof(double) * VIEKF_STAT_WIDTH * n_buckets));
+      h->kp.n_buckets = n_buckets;
+    }
+  }
+  if (h->kp.stats) CK(cudaMemsetAsync(h->kp.stats, 0, sizeof(double) * VIEKF_STAT_WIDTH * n_buckets, h->stream));
+  CK(cudaStreamSynchronize(h->stream));
+  return VIEKF_OK;
+}
+
+int viekf_batch_stats(viekf_batch* h, double* out, int32_t n_buckets) {
+  if (!h || !out || n_buckets < 0 || n_buckets > h->kp.n_buckets) return fail(VIEKF_ERR_ARG, "bad argument");
+  CK(cudaSetDevice(h->device));
+  CK(cudaStreamSynchronize(h->stream));
+  if (n_buckets > 0) CK(cudaMemcpy(out, h->kp.stats, sizeof(double) * VIEKF_STAT_WIDTH * n_buckets, cudaMemcpyDeviceToHost));
+  return VIEKF_OK;
+}
+
+void* viekf_batch_stats_dev_ptr(viekf_batch* h) { return h ? (void*)h->kp.stats : nullptr; }
+
+int viekf_fp64_peak_probe(int32_t device, double* tflops) {
+  if (!tflops) return fail(VIEKF_ERR_ARG, "null pointer");
+  int ndev = 0;
+  if (cudaGetDeviceCount(&ndev) != cudaSuccess || device < 0 || device >= ndev) return fail(VIEKF_ERR_NODEVICE, "no such CUDA device");
+  CK(vk::fp64_probe(device, tflops));
+  return VIEKF_OK;
+}
+
+}  // extern "C"

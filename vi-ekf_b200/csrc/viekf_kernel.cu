@@ -1,0 +1,1352 @@
+// viekf_kernel.cu -- persistent tape executor of the VI-EKF batch engine (sm_100a, FP64).
+//
+// One group of G threads owns one filter instance: its state x and packed-symmetric covariance P are loaded from
+// HBM into shared memory once, every event of the tape slice is applied on chip, and x, P go back to HBM once.
+// Events follow the in-order semantics of include/viekf_batch.h; each handler names the reference code it replaces:
+//   PROP    VIEKF::propagate_state + dynamics + boxplus + fix_depth   (vi_ekf.cpp:262-318, vi_ekf_dyn.cpp:14-135)
+//   UPD     add_measurement bookkeeping + VIEKF::update + h_*          (vi_ekf_meas.cpp:130-147,196-395)
+//   INIT    init_feature                                               (vi_ekf_feat.cpp:6-47)
+//   CLEAR / KEEP  clear_feature / keep_only_features                    (vi_ekf_feat.cpp:50-142)
+//   KFRESET keyframe_reset                                              (vi_ekf_kfr.cpp:56-157)
+//   STAT    RMSE / NEES partial sums (names only in multirotor_sim/mclogger.h:50-52)
+//
+// Structure exploited: the discrete transition is [[A_bb,0],[A_fb,blkdiag(A_ff,i)]], so
+//   P'_bb = A_bb P_bb A_bb^T,  Y_i = A_fb,i P_bb + A_ff,i P_fb,i,  P'_fb,i = Y_i A_bb^T,
+//   P'_ff,ij = Y_i A_fb,j^T + (A_fb,i P_bf,j + A_ff,i P_ff,ij) A_ff,j^T            (+ G_d Qu G_d^T + Qx)
+// is evaluated in place block by block, and every H has <= 6 non-zero columns, so the Joseph update
+//   P' = (I-KH) P (I-KH)^T + K R K^T = P - K(HP) - (HP)^T K^T + K S K^T
+// is a symmetric rank update.  Only the live part n = 16 + 3 len of the MAX_DX system is touched: the dead slots
+// of the reference's dense product contribute exact zeros.
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include "viekf_engine.h"
+#include "viekf_math.cuh"
+#include "../../include/viekf_noise.h"
+
+namespace vk {
+
+// ------------------------------------------------------------------------------------------------------------------
+// shared-memory layout of one filter (offsets in doubles), a function of N only
+// ------------------------------------------------------------------------------------------------------------------
+struct Layout {
+  int x, P, lam, dx, Abd, T, Ac, Gb, Afd, Gd, Y, upd, small, ids, total;
+};
+__host__ __device__ inline int ev2(int v) { return (v + 1) & ~1; }
+__host__ __device__ inline Layout make_layout(int N) {
+  Layout L;
+  const int nmax = 16 + 3 * N;
+  int o = 0;
+  L.x = o;     o += ev2(17 + 5 * N);
+  L.P = o;     o += ev2(nmax * (nmax + 1) / 2);
+  L.lam = o;   o += ev2(nmax);
+  L.dx = o;    o += ev2(nmax);
+  L.Abd = o;   o += 256;
+  L.T = o;     o += 256;
+  L.Ac = o;    o += 144;
+  L.Gb = o;    o += 54 + 2;
+  L.Afd = o;   o += ev2(3 * N * 19);
+  L.Gd = o;    o += ev2(nmax * 6);
+  L.Y = o;     o += ev2(3 * N * 16);  // also the continuous feature blocks (27 per feature) before discretisation
+  L.upd = L.Afd;                      // update workspace (PHt, K, KS: 9 n) overlays the propagate workspace
+  const int upd_end = L.upd + ev2(9 * nmax);
+  if (upd_end > o) o = upd_end;
+  L.small = o; o += 64;
+  L.ids = o;   o += ev2(N + 12);  // ids[N] + rm[N] + scalars[SC_COUNT + 9], as int32
+  L.total = ev2(o);
+  return L;
+}
+
+size_t smem_bytes_per_filter(int N) { return (size_t)make_layout(N).total * sizeof(double); }
+
+int group_size_for(int N) {
+  if (N <= 1) return 32;
+  if (N <= 6) return 64;
+  if (N <= 16) return 128;
+  return 256;
+}
+
+// scalars kept as int32 behind the ids array
+enum { SC_LEN = 0, SC_NEXT = 1, SC_STARTED = 2, SC_FLAGS = 3, SC_NGATED = 4, SC_NFIX = 5, SC_NNAN = 6, SC_NKF = 7, SC_TMP0 = 8, SC_TMP1 = 9,
+       SC_COUNT = 10 };
+
+template <int G>
+struct Ctx {
+  double *x, *P, *lam, *dx, *Abd, *T, *Ac, *Gb, *Afd, *Gd, *Y, *upd, *sm;
+  int *ids, *rm, *sc;
+  double* tcur;  // filter time lives in sm[63]
+  int tid, gi;
+  int64_t b;
+  __device__ __forceinline__ void sync() const {
+    if (G == 32)
+      __syncwarp();
+    else
+      asm volatile("bar.sync %0, %1;" ::"r"(gi + 1), "r"(G) : "memory");
+  }
+};
+
+// small scratch slots inside sm[64]
+enum { SM_ZV = 0 /*8*/, SM_HC = 8 /*18*/, SM_S = 26 /*9*/, SM_SI = 35 /*9*/, SM_RES = 44 /*4*/, SM_ER = 44 /*16, STAT only*/, SM_T = 63 };
+
+// ------------------------------------------------------------------------------------------------------------------
+// PROP
+// ------------------------------------------------------------------------------------------------------------------
+template <int G>
+__device__ void base_dynamics(const Ctx<G>& c, const KParams& p, const double* ub) {
+  const double* x = c.x;
+  V3 vel = ld3(x + 3);
+  Q4 q = ldq(x + 6);
+  V3 acc = mk3(ub[0] - x[10], ub[1] - x[11], ub[2] - x[12]);
+  V3 om = mk3(ub[3] - x[13], ub[4] - x[14], ub[5] - x[15]);
+  const double mu = x[16];
+  double R[9];
+  Rmat(q, R);
+  V3 gB = rotp(q, mk3(0, 0, 9.80665));
+  V3 pd = rota(q, vel);
+  V3 oxv = cross(om, vel);
+  V3 vd;
+  if (p.use_drag)
+    vd = mk3(gB.x - oxv.x - mu * vel.x, gB.y - oxv.y - mu * vel.y, acc.z + gB.z - oxv.z);
+  else
+    vd = acc + gB - oxv;
+  double* dx = c.dx;
+  dx[0] = pd.x; dx[1] = pd.y; dx[2] = pd.z;
+  dx[3] = vd.x; dx[4] = vd.y; dx[5] = vd.z;
+  dx[6] = om.x; dx[7] = om.y; dx[8] = om.z;
+  for (int i = 9; i < 16; i++) dx[i] = 0.0;
+  double* A = c.Ac;  // 9 x 16 row-major (rows POS, VEL, ATT of the continuous A)
+  for (int i = 0; i < 144; i++) A[i] = 0.0;
+  double* Gb = c.Gb;  // 9 x 6
+  for (int i = 0; i < 54; i++) Gb[i] = 0.0;
+  const double sv[9] = {0, -vel.z, vel.y, vel.z, 0, -vel.x, -vel.y, vel.x, 0};
+  const double so[9] = {0, -om.z, om.y, om.z, 0, -om.x, -om.y, om.x, 0};
+  const double sg[9] = {0, -gB.z, gB.y, gB.z, 0, -gB.x, -gB.y, gB.x, 0};
+  for (int r = 0; r < 3; r++)
+    for (int cc = 0; cc < 3; cc++) {
+      A[r * 16 + 3 + cc] = R[cc * 3 + r];  // (POS,VEL) = R^T
+      double s = 0;
+      for (int k = 0; k < 3; k++) s += (-R[k * 3 + r]) * sv[k * 3 + cc];
+      A[r * 16 + 6 + cc] = s;  // (POS,ATT) = -R^T [v]x
+      A[(3 + r) * 16 + 3 + cc] = -so[r * 3 + cc];
+      A[(3 + r) * 16 + 6 + cc] = sg[r * 3 + cc];
+      A[(3 + r) * 16 + 12 + cc] = -sv[r * 3 + cc];
+      A[(6 + r) * 16 + 6 + cc] = -so[r * 3 + cc];
+      Gb[(3 + r) * 6 + 3 + cc] = -sv[r * 3 + cc];
+    }
+  for (int r = 0; r < 3; r++) {
+    A[(6 + r) * 16 + 12 + r] = -1.0;
+    Gb[(6 + r) * 6 + 3 + r] = -1.0;
+  }
+  if (p.use_drag) {
+    A[3 * 16 + 3] += -mu;
+    A[4 * 16 + 4] += -mu;
+    A[5 * 16 + 11] = -1.0;
+    A[3 * 16 + 15] = -vel.x;
+    A[4 * 16 + 15] = -vel.y;
+    Gb[5 * 6 + 2] = -1.0;
+  } else {
+    for (int r = 0; r < 3; r++) {
+      A[(3 + r) * 16 + 9 + r] = -1.0;
+      Gb[(3 + r) * 6 + r] = -1.0;
+    }
+  }
+}
+
+// continuous feature blocks of feature i: out[27] = A(f,VEL) 3x3 | A(f,B_G) 3x3 | A(f,f) 3x3, plus xdot (vi_ekf_dyn.cpp:96-134)
+template <int G>
+__device__ void feature_dynamics(const Ctx<G>& c, const KParams& p, const double* ub, int i) {
+  const double* x = c.x;
+  V3 vel = ld3(x + 3);
+  V3 om = mk3(ub[3] - x[13], ub[4] - x[14], ub[5] - x[15]);
+  Q4 qbc = ldq(p.qbc);
+  V3 pbc = ld3(p.pbc);
+  V3 vc = rotp(qbc, vel + cross(om, pbc));
+  V3 oc = rotp(qbc, om);
+  Q4 qz = ldq(x + 17 + 5 * i);
+  const double rho = x[17 + 5 * i + 4];
+  const double rho2 = rho * rho;
+  V3 ze, T0, T1;
+  zeta_T(qz, ze, T0, T1);
+  V3 zxv = cross(ze, vc);
+  V3 w = oc + rho * zxv;
+  double* dx = c.dx + 16 + 3 * i;
+  dx[0] = -dot(T0, w);
+  dx[1] = -dot(T1, w);
+  dx[2] = rho2 * dot(ze, vc);
+  double* o = c.Y + 27 * i;
+  const double sz[9] = {0, -ze.z, ze.y, ze.z, 0, -ze.x, -ze.y, ze.x, 0};
+  const double svc[9] = {0, -vc.z, vc.y, vc.z, 0, -vc.x, -vc.y, vc.x, 0};
+  const double sw[9] = {0, -w.z, w.y, w.z, 0, -w.x, -w.y, w.x, 0};
+  double M1[9];  // [zeta]x R_bc
+  for (int r = 0; r < 3; r++)
+    for (int cc = 0; cc < 3; cc++) {
+      double s = 0;
+      for (int k = 0; k < 3; k++) s += sz[r * 3 + k] * p.Rbc[k * 3 + cc];
+      M1[r * 3 + cc] = s;
+    }
+  const double Tm[6] = {T0.x, T0.y, T0.z, T1.x, T1.y, T1.z};
+  const double zv[3] = {ze.x, ze.y, ze.z};
+  // M2 = rho [zeta]x R_bc [p_bc]x - R_bc, through the host-precomputed R_bc [p_bc]x
+  double M2[9];
+  for (int r = 0; r < 3; r++)
+    for (int cc = 0; cc < 3; cc++) {
+      double s = 0;
+      for (int k = 0; k < 3; k++) s += sz[r * 3 + k] * p.RbcSp[k * 3 + cc];
+      M2[r * 3 + cc] = rho * s - p.Rbc[r * 3 + cc];
+    }
+  double Mzz[9];
+  for (int r = 0; r < 3; r++)
+    for (int cc = 0; cc < 3; cc++) {
+      double s = 0;
+      for (int k = 0; k < 3; k++) s += svc[r * 3 + k] * sz[k * 3 + cc];
+      Mzz[r * 3 + cc] = sw[r * 3 + cc] + rho * s;
+    }
+  for (int a = 0; a < 2; a++) {
+    const double* Ta = Tm + 3 * a;
+    for (int cc = 0; cc < 3; cc++) {
+      o[a * 3 + cc] = -rho * (Ta[0] * M1[cc] + Ta[1] * M1[3 + cc] + Ta[2] * M1[6 + cc]);
+      o[9 + a * 3 + cc] = -(Ta[0] * M2[cc] + Ta[1] * M2[3 + cc] + Ta[2] * M2[6 + cc]);
+    }
+    double tm[3];
+    for (int cc = 0; cc < 3; cc++) tm[cc] = Ta[0] * Mzz[cc] + Ta[1] * Mzz[3 + cc] + Ta[2] * Mzz[6 + cc];
+    for (int bb = 0; bb < 2; bb++) o[18 + a * 3 + bb] = -(tm[0] * Tm[3 * bb] + tm[1] * Tm[3 * bb + 1] + tm[2] * Tm[3 * bb + 2]);
+    o[18 + a * 3 + 2] = -(Ta[0] * zxv.x + Ta[1] * zxv.y + Ta[2] * zxv.z);
+  }
+  for (int cc = 0; cc < 3; cc++) {
+    o[6 + cc] = rho2 * (zv[0] * p.Rbc[cc] + zv[1] * p.Rbc[3 + cc] + zv[2] * p.Rbc[6 + cc]);
+    o[15 + cc] = rho2 * (zv[0] * p.RbcSp[cc] + zv[1] * p.RbcSp[3 + cc] + zv[2] * p.RbcSp[6 + cc]);
+  }
+  double zs[3];
+  for (int cc = 0; cc < 3; cc++) zs[cc] = zv[0] * svc[cc] + zv[1] * svc[3 + cc] + zv[2] * svc[6 + cc];
+  for (int bb = 0; bb < 2; bb++) o[24 + bb] = rho2 * (zs[0] * Tm[3 * bb] + zs[1] * Tm[3 * bb + 1] + zs[2] * Tm[3 * bb + 2]);
+  o[26] = 2 * rho * dot(ze, vc);
+}
+
+// fix_depth (vi_ekf_helper.cpp:128-156) for feature i
+template <int G>
+__device__ __forceinline__ void fix_depth_one(const Ctx<G>& c, const KParams& p, int i) {
+  double* rho = c.x + 17 + 5 * i + 4;
+  const int d = 16 + 3 * i + 2;
+  const double reset = 1.0 / (2.0 * p.min_depth);
+  double r = *rho;
+  uint32_t fl = 0;
+  int nfix = 0;
+  if (r != r) {
+    r = reset;
+    fl |= VIEKF_FLAG_DEPTH_NAN_FIXED;
+    nfix++;
+  }
+  if (r < 0.0) {
+    const double err = reset - r;
+    c.P[plo(d, d)] += err * err;
+    r = reset;
+    fl |= VIEKF_FLAG_DEPTH_NEG_FIXED;
+    nfix++;
+  } else if (r > 1e2) {
+    c.P[plo(d, d)] = p.P0f[2];
+    r = reset;
+    fl |= VIEKF_FLAG_DEPTH_BIG_FIXED;
+    nfix++;
+  }
+  if (nfix) {
+    *rho = r;
+    atomicOr((unsigned*)&c.sc[SC_FLAGS], fl);
+    atomicAdd(&c.sc[SC_NFIX], nfix);
+  }
+}
+
+// x <- x [+] d  (vi_ekf_helper.cpp:88-98): base part by the last thread of the group, feature i by thread i
+template <int G>
+__device__ __forceinline__ void boxplus_inplace(const Ctx<G>& c, const double* d, double s, int len) {
+  if (c.tid == G - 1) {
+    double* x = c.x;
+    for (int k = 0; k < 6; k++) x[k] += d[k] * s;
+    Q4 q = otimes(ldq(x + 6), qexp(mk3(d[6] * s, d[7] * s, d[8] * s)));
+    stq(x + 6, q);
+    for (int k = 0; k < 7; k++) x[10 + k] += d[9 + k] * s;
+  }
+  for (int i = c.tid; i < len; i += G) {
+    double* xf = c.x + 17 + 5 * i;
+    const double* df = d + 16 + 3 * i;
+    Q4 q = qfeat_boxplus(ldq(xf), df[0] * s, df[1] * s);
+    stq(xf, q);
+    xf[4] += df[2] * s;
+  }
+}
+
+template <int G>
+__device__ void ev_propagate(Ctx<G>& c, const KParams& p, const viekf_event& E) {
+  // uniform control flow: every thread evaluates the same guards from shared state (vi_ekf.cpp:274-289)
+  const int started = c.sc[SC_STARTED];
+  const double tcur = *c.tcur;
+  const double dt = E.t - tcur;
+  if (!started) {
+    c.sync();
+    if (c.tid == 0) {
+      c.sc[SC_STARTED] = 1;
+      *c.tcur = E.t;
+    }
+    c.sync();
+    return;
+  }
+  if (fabs(dt) < 1e-6) return;
+  if (dt < 0) {
+    if (c.tid == 0) c.sc[SC_FLAGS] |= VIEKF_FLAG_BACKWARD_DT;
+    c.sync();
+    return;
+  }
+  const int len = c.sc[SC_LEN];
+  const int n = 16 + 3 * len;
+  const double* zv = c.sm + SM_ZV;
+  // IMU sample into the body frame (vi_ekf.cpp:265-267)
+  double ub[6];
+  {
+    Q4 qbu = ldq(p.qbu);
+    V3 a = rota(qbu, mk3(zv[0], zv[1], zv[2])), g = rota(qbu, mk3(zv[3], zv[4], zv[5]));
+    ub[0] = a.x; ub[1] = a.y; ub[2] = a.z; ub[3] = g.x; ub[4] = g.y; ub[5] = g.z;
+  }
+  // ---- phase A: continuous dynamics and Jacobian blocks ----
+  if (c.tid == G - 1) base_dynamics(c, p, ub);
+  for (int i = c.tid; i < len; i += G) feature_dynamics(c, p, ub, i);
+  c.sync();
+  // ---- phase B: discretisation, one row of [A_d | G_d] per task (vi_ekf.cpp:302-303) ----
+  const double h2 = dt * dt / 2.0, h6 = dt * dt / 6.0, hd2 = dt / 2.0;
+  for (int task = c.tid; task < n; task += G) {
+    if (task < 16) {
+      const int r = task;
+      double* Ad = c.Abd + r * 16;
+      double* Gd = c.Gd + r * 6;
+      if (r >= 9) {
+        for (int k = 0; k < 16; k++) Ad[k] = (k == r) ? 1.0 : 0.0;
+        for (int q = 0; q < 6; q++) Gd[q] = 0.0;
+      } else {
+        const double* Ar = c.Ac + r * 16;
+        double m[9];
+        for (int cc = 0; cc < 16; cc++) {
+          double aa = 0;
+          for (int k = 3; k < 9; k++) aa += Ar[k] * c.Ac[k * 16 + cc];
+          const double id = (cc == r) ? 1.0 : 0.0;
+          Ad[cc] = (id + Ar[cc] * dt) + aa * h2;
+          if (cc < 9) m[cc] = (id + Ar[cc] * hd2) + aa * h6;
+        }
+        for (int q = 0; q < 6; q++) {
+          double s = 0;
+          for (int k = 0; k < 9; k++) s += m[k] * c.Gb[k * 6 + q];
+          Gd[q] = s * dt;
+        }
+      }
+    } else {
+      const int fr = task - 16, i = fr / 3, a = fr - 3 * i;
+      const double* F = c.Y + 27 * i;  // Afv | Afg | Aff (continuous)
+      double* Ad = c.Afd + fr * 19;
+      double* Gd = c.Gd + task * 6;
+      double mfb[9];
+      for (int cc = 0; cc < 3; cc++) {
+        Ad[cc] = 0.0;
+        mfb[cc] = 0.0;
+      }
+      for (int cc = 3; cc < 16; cc++) {
+        double aa = 0;
+        for (int k = 0; k < 3; k++) aa += F[a * 3 + k] * c.Ac[(3 + k) * 16 + cc];
+        double ac = 0.0;
+        if (cc < 6) {
+          for (int k = 0; k < 3; k++) aa += F[18 + a * 3 + k] * F[k * 3 + (cc - 3)];
+          ac = F[a * 3 + (cc - 3)];
+        } else if (cc >= 12 && cc < 15) {
+          for (int k = 0; k < 3; k++) aa += F[18 + a * 3 + k] * F[9 + k * 3 + (cc - 12)];
+          ac = F[9 + a * 3 + (cc - 12)];
+        }
+        Ad[cc] = ac * dt + aa * h2;
+        if (cc < 9) mfb[cc] = ac * hd2 + aa * h6;
+      }
+      double mff[3];
+      for (int bb = 0; bb < 3; bb++) {
+        double aa = 0;
+        for (int k = 0; k < 3; k++) aa += F[18 + a * 3 + k] * F[18 + k * 3 + bb];
+        const double id = (a == bb) ? 1.0 : 0.0;
+        Ad[16 + bb] = (id + F[18 + a * 3 + bb] * dt) + aa * h2;
+        mff[bb] = (id + F[18 + a * 3 + bb] * hd2) + aa * h6;
+      }
+      for (int q = 0; q < 6; q++) {
+        double s = 0;
+        for (int k = 3; k < 9; k++) s += mfb[k] * c.Gb[k * 6 + q];
+        if (q >= 3)
+          for (int k = 0; k < 3; k++) s += mff[k] * F[9 + k * 3 + (q - 3)];
+        Gd[q] = s * dt;
+      }
+    }
+  }
+  c.sync();
+  // ---- phase C: Y = A_fb P_bb + A_ff P_fb (3len x 16) and T = A_bb P_bb (16 x 16); reads the old P only ----
+  const double* P = c.P;
+  for (int task = c.tid; task < 48 * len + 256; task += G) {
+    if (task < 48 * len) {
+      const int fr = task >> 4, cc = task & 15, i = fr / 3;
+      const double* Ad = c.Afd + fr * 19;
+      double s = 0;
+#pragma unroll
+      for (int k = 3; k < 16; k++) s += Ad[k] * P[psym(k, cc)];
+      const int f0 = 16 + 3 * i;
+#pragma unroll
+      for (int k = 0; k < 3; k++) s += Ad[16 + k] * P[plo(f0 + k, cc)];
+      c.Y[task] = s;
+    } else {
+      const int t2 = task - 48 * len, r = t2 >> 4, cc = t2 & 15;
+      double s = 0;
+#pragma unroll
+      for (int k = 0; k < 16; k++) s += c.Abd[r * 16 + k] * P[psym(k, cc)];
+      c.T[t2] = s;
+    }
+  }
+  c.sync();
+  // ---- phase D: P'_ff blocks in place, and P'_bb from T ----
+  const int nb = (len * (len + 1)) >> 1;
+  for (int task = c.tid; task < nb + 136; task += G) {
+    if (task < nb) {
+      int i = (int)((sqrtf(8.0f * (float)task + 1.0f) - 1.0f) * 0.5f);
+      while (((i + 1) * (i + 2) >> 1) <= task) i++;
+      while (((i * (i + 1)) >> 1) > task) i--;
+      const int j = task - ((i * (i + 1)) >> 1);
+      const int fi = 16 + 3 * i, fj = 16 + 3 * j;
+      const double* Ai = c.Afd + 3 * i * 19;
+      const double* Aj = c.Afd + 3 * j * 19;
+      const double* Yi = c.Y + 3 * i * 16;
+      double Z[9];
+#pragma unroll
+      for (int a = 0; a < 3; a++)
+#pragma unroll
+        for (int bb = 0; bb < 3; bb++) {
+          double s = 0;
+          const double* Pr = c.P + plo(fj + bb, 0);
+#pragma unroll
+          for (int k = 3; k < 16; k++) s += Ai[a * 19 + k] * Pr[k];
+#pragma unroll
+          for (int k = 0; k < 3; k++) s += Ai[a * 19 + 16 + k] * c.P[psym(fi + k, fj + bb)];
+          Z[a * 3 + bb] = s;
+        }
+      double o[9];
+#pragma unroll
+      for (int a = 0; a < 3; a++)
+#pragma unroll
+        for (int bb = 0; bb < 3; bb++) {
+          double s = 0;
+#pragma unroll
+          for (int k = 3; k < 16; k++) s += Yi[a * 16 + k] * Aj[bb * 19 + k];
+#pragma unroll
+          for (int k = 0; k < 3; k++) s += Z[a * 3 + k] * Aj[bb * 19 + 16 + k];
+#pragma unroll
+          for (int q = 0; q < 6; q++) s += (c.Gd[(fi + a) * 6 + q] * p.Qu[q]) * c.Gd[(fj + bb) * 6 + q];
+          o[a * 3 + bb] = s;
+        }
+      if (i == j) {
+        for (int a = 0; a < 3; a++)
+          for (int bb = 0; bb <= a; bb++) c.P[plo(fi + a, fj + bb)] = o[a * 3 + bb] + (a == bb ? p.Qxf[a] : 0.0);
+      } else {
+        for (int a = 0; a < 3; a++)
+          for (int bb = 0; bb < 3; bb++) c.P[plo(fi + a, fj + bb)] = o[a * 3 + bb];
+      }
+    } else {
+      const int e = task - nb;
+      int r = (int)((sqrtf(8.0f * (float)e + 1.0f) - 1.0f) * 0.5f);
+      while (((r + 1) * (r + 2) >> 1) <= e) r++;
+      while (((r * (r + 1)) >> 1) > e) r--;
+      const int cc = e - ((r * (r + 1)) >> 1);
+      double s = 0;
+#pragma unroll
+      for (int k = 0; k < 16; k++) s += c.T[r * 16 + k] * c.Abd[cc * 16 + k];
+#pragma unroll
+      for (int q = 0; q < 6; q++) s += (c.Gd[r * 6 + q] * p.Qu[q]) * c.Gd[cc * 6 + q];
+      if (r == cc) s += p.Qx[r];
+      c.P[e] = s;
+    }
+  }
+  c.sync();
+  // ---- phase E: P'_fb = Y A_bb^T (+ G_d Qu G_d^T), state boxplus ----
+  for (int task = c.tid; task < 48 * len; task += G) {
+    const int fr = task >> 4, cc = task & 15;
+    double s = 0;
+#pragma unroll
+    for (int k = 0; k < 16; k++) s += c.Y[fr * 16 + k] * c.Abd[cc * 16 + k];
+#pragma unroll
+    for (int q = 0; q < 6; q++) s += (c.Gd[(16 + fr) * 6 + q] * p.Qu[q]) * c.Gd[cc * 6 + q];
+    c.P[plo(16 + fr, cc)] = s;
+  }
+  boxplus_inplace(c, c.dx, dt, len);
+  if (c.tid == 0) *c.tcur = E.t;
+  c.sync();
+  // ---- phase F: fix_depth ----
+  for (int i = c.tid; i < len; i += G) fix_depth_one(c, p, i);
+  c.sync();
+}
+
+// ------------------------------------------------------------------------------------------------------------------
+// feature management
+// ------------------------------------------------------------------------------------------------------------------
+template <int G>
+__device__ int find_feature(const Ctx<G>& c, int id) {
+  const int len = c.sc[SC_LEN];
+  for (int i = 0; i < len; i++)
+    if (c.ids[i] == id) return i;
+  return -1;
+}
+
+// init_feature (vi_ekf_feat.cpp:6-47).  Returns (uniformly) whether a slot was available.
+template <int G>
+__device__ bool do_init_feature(Ctx<G>& c, const KParams& p, double l0, double l1, double depth) {
+  const int len = c.sc[SC_LEN];
+  if (len >= p.N) return false;
+  const int r0 = 16 + 3 * len;
+  c.sync();
+  if (c.tid == 0) {
+    const double lc0 = l0 - p.cc[0], lc1 = l1 - p.cc[1];
+    V3 z = mk3(lc0, lc1 * (p.fl[1] / p.fl[0]), p.fl[0]);
+    const double nz = norm(z);
+    z = mk3(z.x / nz, z.y / nz, z.z / nz);
+    Q4 q = from_two_unit_vectors(mk3(0, 0, 1), z);
+    double d = depth;
+    if (d != d) d = 2.0 * p.min_depth;
+    double* xf = c.x + 17 + 5 * len;
+    stq(xf, q);
+    xf[4] = 1.0 / d;
+    c.ids[len] = c.sc[SC_NEXT];
+    c.sc[SC_NEXT] += 1;
+    c.sc[SC_LEN] = len + 1;
+  }
+  double* Pn = c.P + plo(r0, 0);
+  const int cnt = plo(r0 + 3, 0) - plo(r0, 0);
+  for (int e = c.tid; e < cnt; e += G) Pn[e] = 0.0;
+  c.sync();
+  if (c.tid < 3) c.P[plo(r0 + c.tid, r0 + c.tid)] = p.P0f[c.tid];
+  c.sync();
+  return true;
+}
+
+// clear_feature (vi_ekf_feat.cpp:50-73): order-preserving compaction of x and of the packed P, in place.
+template <int G>
+__device__ void do_clear_feature(Ctx<G>& c, const KParams& p, int local) {
+  const int len = c.sc[SC_LEN];
+  if (local < 0 || local >= len) return;
+  c.sync();
+  const int nl = len - 1;
+  // x tail
+  {
+    const int dst0 = 17 + 5 * local, cnt = 5 * (nl - local);
+    for (int base = 0; base < cnt; base += G) {
+      const int e = base + c.tid;
+      double v = 0;
+      if (e < cnt) v = c.x[dst0 + 5 + e];
+      c.sync();
+      if (e < cnt) c.x[dst0 + e] = v;
+      c.sync();
+    }
+  }
+  // P: new(i,j) = old(i + 3[i>=d0], j + 3[j>=d0]); destination index <= source index, so chunks in ascending order with
+  // a read-all / barrier / write-all cycle never overwrite an element that is still to be read.
+  const int d0 = 16 + 3 * local;
+  const int nn = 16 + 3 * nl;
+  const int first = plo(d0, 0), last = plo(nn, 0);
+  constexpr int PER = 4;
+  for (int base = first; base < last; base += G * PER) {
+    double v[PER];
+#pragma unroll
+    for (int u = 0; u < PER; u++) {
+      const int e = base + u * G + c.tid;
+      v[u] = 0;
+      if (e < last) {
+        int i = (int)((sqrtf(8.0f * (float)e + 1.0f) - 1.0f) * 0.5f);
+        while (((i + 1) * (i + 2) >> 1) <= e) i++;
+        while (((i * (i + 1)) >> 1) > e) i--;
+        const int j = e - ((i * (i + 1)) >> 1);
+        v[u] = c.P[plo(i + 3, j >= d0 ? j + 3 : j)];
+      }
+    }
+    c.sync();
+#pragma unroll
+    for (int u = 0; u < PER; u++) {
+      const int e = base + u * G + c.tid;
+      if (e < last) c.P[e] = v[u];
+    }
+    c.sync();
+  }
+  if (c.tid == 0) {
+    for (int i = local; i < nl; i++) c.ids[i] = c.ids[i + 1];
+    c.sc[SC_LEN] = nl;
+  }
+  c.sync();
+}
+
+// keyframe_reset (vi_ekf_kfr.cpp:56-157): zero position, strip yaw, P = N P N^T, accumulate the global pose / cov.
+template <int G>
+__device__ void do_keyframe_reset(Ctx<G>& c, const KParams& p) {
+  const int len = c.sc[SC_LEN];
+  const int n = 16 + 3 * len;
+  c.sync();
+  double* Nb = c.sm + SM_HC;  // 9 doubles, row-major
+  if (c.tid == 0) {
+    FilterMeta& M = p.meta[c.b];
+    double* x = c.x;
+    double ecov[36];
+    for (int k = 0; k < 36; k++) ecov[k] = 0.0;
+    for (int i = 0; i < 3; i++)
+      for (int j = 0; j < 3; j++) ecov[i + 6 * j] = c.P[psym(i, j)];
+    ecov[5 + 6 * 5] = c.P[plo(8, 8)];
+    V3 et = ld3(x);
+    x[0] = x[1] = x[2] = 0.0;
+    Q4 q = ldq(x + 6);
+    const double yaw = qyaw(q), roll = qroll(q), pitch = qpitch(q);
+    Q4 qe = from_euler(0, 0, yaw);
+    stq(x + 6, from_euler(roll, pitch, 0.0));
+    const double cp = cos(roll), sp = sin(roll), tt = tan(pitch);
+    Nb[0] = 1; Nb[1] = sp * tt; Nb[2] = cp * tt;
+    Nb[3] = 0; Nb[4] = cp * cp; Nb[5] = -cp * sp;
+    Nb[6] = 0; Nb[7] = -cp * sp; Nb[8] = sp * sp;
+    // global covariance: P_new = P_prev + Adj^T cov Adj, Adj = [[R,[t]x R],[0,R]] of the current node pose
+    Q4 nq = ldq(M.node_q);
+    V3 nt = ld3(M.node_t);
+    double R[9];
+    Rmat(nq, R);
+    const double st[9] = {0, -nt.z, nt.y, nt.z, 0, -nt.x, -nt.y, nt.x, 0};
+    double Adj[36];
+    for (int k = 0; k < 36; k++) Adj[k] = 0.0;
+    for (int i = 0; i < 3; i++)
+      for (int j = 0; j < 3; j++) {
+        double s = 0;
+        for (int k = 0; k < 3; k++) s += st[i * 3 + k] * R[k * 3 + j];
+        Adj[i + 6 * j] = R[i * 3 + j];
+        Adj[i + 6 * (j + 3)] = s;
+        Adj[(i + 3) + 6 * (j + 3)] = R[i * 3 + j];
+      }
+    double Tm[36];
+    for (int i = 0; i < 6; i++)
+      for (int j = 0; j < 6; j++) {
+        double s = 0;
+        for (int k = 0; k < 6; k++) s += Adj[k + 6 * i] * ecov[k + 6 * j];
+        Tm[i + 6 * j] = s;
+      }
+    for (int i = 0; i < 6; i++)
+      for (int j = 0; j < 6; j++) {
+        double s = 0;
+        for (int k = 0; k < 6; k++) s += Tm[i + 6 * k] * Adj[k + 6 * j];
+        M.gcov[i + 6 * j] += s;
+      }
+    V3 nt2 = nt + rota(nq, et);
+    M.node_t[0] = nt2.x; M.node_t[1] = nt2.y; M.node_t[2] = nt2.z;
+    stq(M.node_q, otimes(nq, qe));
+  }
+  c.sync();
+  // P = N P N^T with N = I except N(POS,POS) = 0 and N(ATT,ATT) = Nb
+  for (int i = c.tid; i < n; i += G) {
+    if (i < 3) {
+      for (int j = 0; j <= i; j++) c.P[plo(i, j)] = 0.0;
+    } else if (i < 6) {
+      for (int j = 0; j < 3; j++) c.P[plo(i, j)] = 0.0;
+      // column part: rows 6..8 against this column i (i in 3..5)
+      double v[3], o[3];
+      for (int a = 0; a < 3; a++) v[a] = c.P[plo(6 + a, i)];
+      for (int a = 0; a < 3; a++) o[a] = Nb[a * 3] * v[0] + Nb[a * 3 + 1] * v[1] + Nb[a * 3 + 2] * v[2];
+      for (int a = 0; a < 3; a++) c.P[plo(6 + a, i)] = o[a];
+    } else if (i == 6) {
+      for (int r = 6; r < 9; r++)
+        for (int j = 0; j < 3; j++) c.P[plo(r, j)] = 0.0;
+      double A[9], B[9];
+      for (int a = 0; a < 3; a++)
+        for (int bb = 0; bb < 3; bb++) A[a * 3 + bb] = c.P[psym(6 + a, 6 + bb)];
+      for (int a = 0; a < 3; a++)
+        for (int bb = 0; bb < 3; bb++) B[a * 3 + bb] = Nb[a * 3] * A[bb] + Nb[a * 3 + 1] * A[3 + bb] + Nb[a * 3 + 2] * A[6 + bb];
+      for (int a = 0; a < 3; a++)
+        for (int bb = 0; bb <= a; bb++)
+          c.P[plo(6 + a, 6 + bb)] = B[a * 3] * Nb[bb * 3] + B[a * 3 + 1] * Nb[bb * 3 + 1] + B[a * 3 + 2] * Nb[bb * 3 + 2];
+    } else if (i >= 9) {
+      for (int j = 0; j < 3; j++) c.P[plo(i, j)] = 0.0;
+      double v[3];
+      for (int a = 0; a < 3; a++) v[a] = c.P[plo(i, 6 + a)];
+      for (int a = 0; a < 3; a++) c.P[plo(i, 6 + a)] = Nb[a * 3] * v[0] + Nb[a * 3 + 1] * v[1] + Nb[a * 3 + 2] * v[2];
+    }
+  }
+  c.sync();
+}
+
+// keep_only_features (vi_ekf_feat.cpp:81-142)
+template <int G>
+__device__ void do_keep_only(Ctx<G>& c, const KParams& p, const int32_t* feats, int nf) {
+  c.sync();
+  if (c.tid == 0) {
+    const int len = c.sc[SC_LEN];
+    const int nkf = c.sc[SC_NKF];
+    const int32_t* kf = p.kf_ids + c.b * KF_CAP;
+    int nrm = 0, overlap = 0;
+    for (int l = 0; l < len; l++) {
+      bool keep = false;
+      for (int i = 0; i < nf; i++)
+        if (c.ids[l] == feats[i]) {
+          keep = true;
+          if (p.use_kfreset)
+            for (int j = 0; j < nkf; j++)
+              if (kf[j] == feats[i]) {
+                overlap++;
+                break;
+              }
+          break;
+        }
+      if (!keep) c.rm[nrm++] = c.ids[l];
+    }
+    c.sc[SC_TMP0] = nrm;
+    c.sc[SC_TMP1] = overlap;
+  }
+  c.sync();
+  const int nrm = c.sc[SC_TMP0];
+  const int overlap = c.sc[SC_TMP1];
+  for (int k = 0; k < nrm; k++) do_clear_feature(c, p, find_feature(c, c.rm[k]));
+  const int nkf = c.sc[SC_NKF];
+  const bool reset = p.use_kfreset && nkf > 0 && ((double)overlap / (double)nkf < p.kf_thresh);
+  if (reset) do_keyframe_reset(c, p);
+  if (p.use_kfreset && (reset || nkf == 0)) {
+    int32_t* kf = p.kf_ids + c.b * KF_CAP;
+    const int m = nf < KF_CAP ? nf : KF_CAP;
+    for (int i = c.tid; i < m; i += G) kf[i] = feats[i];
+    if (c.tid == 0) c.sc[SC_NKF] = m;
+  }
+  c.sync();
+}
+
+// ------------------------------------------------------------------------------------------------------------------
+// UPD
+// ------------------------------------------------------------------------------------------------------------------
+// symmetric rank update of the packed P:  P_ij += L_ij * ( KS_i.K_j - K_i.H_j - H_i.K_j ),  H = (HP)^T = P H^T
+template <int G, int RD>
+__device__ __forceinline__ void rank_update(const Ctx<G>& c, int n, bool partial) {
+  const double* PHt = c.upd;
+  const double* K = c.upd + 3 * n;
+  const double* KS = c.upd + 6 * n;
+  const int lane = c.tid & 31, warp = c.tid >> 5;
+  constexpr int NW = G / 32;
+  constexpr int RB = 4;
+  int item = 0;
+  for (int i0 = 0; i0 < n; i0 += RB) {
+    const int cmax = min(i0 + RB, n);
+    for (int j0 = 0; j0 < cmax; j0 += 32, item++) {
+      if ((item % NW) != warp) continue;
+      const int j = j0 + lane;
+      if (j >= cmax) continue;
+      double kj[RD], hj[RD];
+#pragma unroll
+      for (int a = 0; a < RD; a++) {
+        kj[a] = K[j * 3 + a];
+        hj[a] = PHt[j * 3 + a];
+      }
+      const double lj = c.lam[j];
+#pragma unroll
+      for (int r = 0; r < RB; r++) {
+        const int i = i0 + r;
+        if (i < n && j <= i) {
+          double d = 0;
+#pragma unroll
+          for (int a = 0; a < RD; a++) d += KS[i * 3 + a] * kj[a] - K[i * 3 + a] * hj[a] - PHt[i * 3 + a] * kj[a];
+          const int e = plo(i, j);
+          if (partial) {
+            const double li = c.lam[i];
+            c.P[e] += ((lj + li) - li * lj) * d;
+          } else {
+            c.P[e] += d;
+          }
+        }
+      }
+    }
+  }
+}
+
+// update(meas) with add_measurement's bookkeeping in front (vi_ekf_meas.cpp:130-147,196-278). Returns meas_result_t.
+template <int G>
+__device__ int ev_update(Ctx<G>& c, const KParams& p, const viekf_event& E) {
+  const double* zv = c.sm + SM_ZV;
+  const int type = E.type, zdim = E.zdim, rd = E.rdim;
+  for (int k = 0; k < zdim; k++)
+    if (zv[k] != zv[k]) return VIEKF_MEAS_NAN;
+  int fi = -1;
+  const bool feat_type = (type == VIEKF_FEAT || type == VIEKF_QZETA || type == VIEKF_DEPTH || type == VIEKF_INV_DEPTH);
+  if (feat_type) {
+    fi = (E.id >= 0) ? find_feature(c, E.id) : -1;
+    if (fi < 0) {
+      if (type == VIEKF_FEAT && E.id >= 0) {
+        do_init_feature(c, p, zv[0], zv[1], E.z[4]);
+        return VIEKF_MEAS_NEW_FEATURE;
+      }
+      return VIEKF_MEAS_INVALID;  // the reference would index the state with -1 here (UB)
+    }
+  }
+  const int len = c.sc[SC_LEN];
+  const int n = 16 + 3 * len;
+  double* Hc = c.sm + SM_HC;   // [3][6]
+  double* S = c.sm + SM_S;     // [3][3] row-major
+  double* Si = c.sm + SM_SI;   // [3][3]
+  double* res = c.sm + SM_RES; // [4]
+  int* cols = c.sc + SC_COUNT; // [6] + m + gate + nan
+  c.sync();
+  // ---- h, H (sparse columns), residual: thread 0 ----
+  if (c.tid == 0) {
+    const double* x = c.x;
+    for (int k = 0; k < 18; k++) Hc[k] = 0.0;
+    double zh[4] = {0, 0, 0, 0};
+    double r4[4] = {0, 0, 0, 0};
+    int m = 0;
+    switch (type) {
+      case VIEKF_ACC:
+        if (p.use_drag) {
+          const double mu = x[16];
+          cols[0] = 3; cols[1] = 4; cols[2] = 9; cols[3] = 10; cols[4] = 15;
+          m = 5;
+          zh[0] = -mu * x[3] + x[10];
+          zh[1] = -mu * x[4] + x[11];
+          Hc[0] = -mu; Hc[2] = 1.0; Hc[4] = -x[3];
+          Hc[6 + 1] = -mu; Hc[6 + 3] = 1.0; Hc[6 + 4] = -x[4];
+        } else {
+          V3 gB = rotp(ldq(x + 6), mk3(0, 0, 9.80665));
+          for (int k = 0; k < 6; k++) cols[k] = 6 + k;
+          m = 6;
+          zh[0] = x[10] - gB.x; zh[1] = x[11] - gB.y; zh[2] = x[12] - gB.z;
+          V3 ng = mk3(-gB.x, -gB.y, -gB.z);
+          const double sk[9] = {0, -ng.z, ng.y, ng.z, 0, -ng.x, -ng.y, ng.x, 0};
+          for (int a = 0; a < 3; a++) {
+            for (int k = 0; k < 3; k++) Hc[a * 6 + k] = sk[a * 3 + k];
+            Hc[a * 6 + 3 + a] = 1.0;
+          }
+        }
+        break;
+      case VIEKF_ALT:
+        cols[0] = 2; m = 1; zh[0] = -x[2]; Hc[0] = -1.0;
+        break;
+      case VIEKF_ATT:
+        for (int k = 0; k < 3; k++) { cols[k] = 6 + k; Hc[k * 6 + k] = 1.0; }
+        m = 3;
+        for (int k = 0; k < 4; k++) zh[k] = x[6 + k];
+        break;
+      case VIEKF_POS:
+        for (int k = 0; k < 3; k++) { cols[k] = k; Hc[k * 6 + k] = 1.0; zh[k] = x[k]; }
+        m = 3;
+        break;
+      case VIEKF_VEL:
+        for (int k = 0; k < 3; k++) { cols[k] = 3 + k; Hc[k * 6 + k] = 1.0; zh[k] = x[3 + k]; }
+        m = 3;
+        break;
+      case VIEKF_QZETA:
+        cols[0] = 16 + 3 * fi; cols[1] = cols[0] + 1; m = 2;
+        Hc[0] = 1.0; Hc[6 + 1] = 1.0;
+        for (int k = 0; k < 4; k++) zh[k] = x[17 + 5 * fi + k];
+        break;
+      case VIEKF_FEAT: {
+        cols[0] = 16 + 3 * fi; cols[1] = cols[0] + 1; m = 2;
+        V3 ze, T0, T1;
+        zeta_T(ldq(x + 17 + 5 * fi), ze, T0, T1);
+        const double ez = ze.z;
+        zh[0] = p.fl[0] * ze.x / ez + p.cc[0];
+        zh[1] = p.fl[1] * ze.y / ez + p.cc[1];
+        // H = (1/ez) F ((zeta e_z^T)/ez - I) [zeta]x T_zeta   (vi_ekf_meas.cpp:366)
+        const double zz[3] = {ze.x, ze.y, ze.z};
+        const double sk[9] = {0, -ze.z, ze.y, ze.z, 0, -ze.x, -ze.y, ze.x, 0};
+        const double Tm[6] = {T0.x, T1.x, T0.y, T1.y, T0.z, T1.z};  // 3x2 row-major
+        for (int a = 0; a < 2; a++) {
+          double fb[3], fbs[3];
+          for (int k = 0; k < 3; k++) fb[k] = (1.0 / ez) * p.fl[a] * (((k == 2) ? zz[a] : 0.0) / ez - (a == k ? 1.0 : 0.0));
+          for (int k = 0; k < 3; k++) fbs[k] = fb[0] * sk[k] + fb[1] * sk[3 + k] + fb[2] * sk[6 + k];
+          for (int bb = 0; bb < 2; bb++) Hc[a * 6 + bb] = fbs[0] * Tm[bb] + fbs[1] * Tm[2 + bb] + fbs[2] * Tm[4 + bb];
+        }
+        break;
+      }
+      case VIEKF_DEPTH: {
+        const double rho = x[17 + 5 * fi + 4];
+        cols[0] = 16 + 3 * fi + 2; m = 1;
+        zh[0] = 1.0 / rho;
+        Hc[0] = -1.0 / (rho * rho);
+        break;
+      }
+      case VIEKF_INV_DEPTH:
+        cols[0] = 16 + 3 * fi + 2; m = 1;
+        zh[0] = x[17 + 5 * fi + 4];
+        Hc[0] = 1.0;
+        break;
+      default:  // PIXEL_VEL: empty stub in the reference (vi_ekf_meas.cpp:388-395): zhat = 0, H = 0
+        m = 0;
+        break;
+    }
+    if (type == VIEKF_QZETA) {
+      qfeat_boxminus(ldq(zv), Q4{zh[0], zh[1], zh[2], zh[3]}, r4);
+    } else if (type == VIEKF_ATT) {
+      V3 d = qboxminus(ldq(zv), Q4{zh[0], zh[1], zh[2], zh[3]});
+      r4[0] = d.x; r4[1] = d.y; r4[2] = d.z;
+    } else {
+      for (int k = 0; k < zdim && k < 4; k++) r4[k] = zv[k] - zh[k];
+    }
+    for (int k = 0; k < 4; k++) res[k] = r4[k];
+    cols[6] = m;
+    cols[7] = 0;  // gate
+    cols[8] = 0;  // nan
+    bool hn = false;
+    for (int k = 0; k < 18; k++) hn |= (Hc[k] != Hc[k]);
+    if (hn) cols[8] = 1;
+  }
+  c.sync();
+  if (E.active) {
+    const int m = cols[6];
+    double* PHt = c.upd;
+    double* K = c.upd + 3 * n;
+    double* KS = c.upd + 6 * n;
+    // ---- P H^T: gather of <= 6 columns of P ----
+    for (int i = c.tid; i < n; i += G) {
+      double s[3] = {0, 0, 0};
+      for (int k = 0; k < m; k++) {
+        const double pv = c.P[psym(i, cols[k])];
+        for (int a = 0; a < 3; a++) s[a] += pv * Hc[a * 6 + k];
+      }
+      for (int a = 0; a < 3; a++) PHt[i * 3 + a] = s[a];
+    }
+    c.sync();
+    // ---- S = H P H^T + R, S^-1 by partial-pivot LU (what Eigen's dynamic inverse does), Mahalanobis gate ----
+    if (c.tid == 0) {
+      double a[3][6];
+      for (int i = 0; i < rd; i++)
+        for (int j = 0; j < rd; j++) {
+          double s = 0;
+          for (int k = 0; k < m; k++) s += Hc[i * 6 + k] * PHt[cols[k] * 3 + j];
+          s += E.R[i + j * rd];
+          S[i * 3 + j] = s;
+          a[i][j] = s;
+          a[i][j + rd] = (i == j) ? 1.0 : 0.0;
+        }
+      for (int cc = 0; cc < rd; cc++) {
+        int pv = cc;
+        for (int i = cc + 1; i < rd; i++)
+          if (fabs(a[i][cc]) > fabs(a[pv][cc])) pv = i;
+        if (pv != cc)
+          for (int j = 0; j < 2 * rd; j++) {
+            const double t = a[cc][j];
+            a[cc][j] = a[pv][j];
+            a[pv][j] = t;
+          }
+        for (int i = cc + 1; i < rd; i++) {
+          const double f = a[i][cc] / a[cc][cc];
+          for (int j = cc; j < 2 * rd; j++) a[i][j] -= f * a[cc][j];
+        }
+      }
+      for (int cc = rd - 1; cc >= 0; cc--)
+        for (int j = 0; j < rd; j++) {
+          double s = a[cc][rd + j];
+          for (int k = cc + 1; k < rd; k++) s -= a[cc][k] * a[k][rd + j];
+          a[cc][rd + j] = s / a[cc][cc];
+        }
+      double mahal = 0;
+      for (int j = 0; j < rd; j++) {
+        double s = 0;
+        for (int i = 0; i < rd; i++) {
+          Si[i * 3 + j] = a[i][rd + j];
+          s += res[i] * a[i][rd + j];
+        }
+        mahal += s * res[j];
+      }
+      if (mahal > 9.0) {
+        cols[7] = 1;
+        c.sc[SC_NGATED] += 1;
+      }
+    }
+    c.sync();
+    if (cols[7]) return VIEKF_MEAS_GATED;  // early return: no fix_depth (vi_ekf_meas.cpp:238)
+    // ---- K = P H^T S^-1, K S, state correction lambda o (K r) ----
+    bool bad = false;
+    for (int i = c.tid; i < n; i += G) {
+      double k3[3] = {0, 0, 0};
+      for (int bb = 0; bb < rd; bb++) {
+        double s = 0;
+        for (int a = 0; a < rd; a++) s += PHt[i * 3 + a] * Si[a * 3 + bb];
+        k3[bb] = s;
+        bad |= (s != s);
+      }
+      double d = 0;
+      for (int a = 0; a < rd; a++) d += k3[a] * res[a];
+      for (int a = 0; a < 3; a++) {
+        double s = 0;
+        for (int bb = 0; bb < rd; bb++) s += k3[bb] * S[bb * 3 + a];
+        K[i * 3 + a] = k3[a];
+        KS[i * 3 + a] = (a < rd) ? s : 0.0;
+      }
+      c.dx[i] = p.use_partial ? c.lam[i] * d : d;
+    }
+    if (bad) atomicOr((unsigned*)&cols[8], 1u);
+    c.sync();
+    if (!cols[8]) {
+      boxplus_inplace(c, c.dx, 1.0, len);
+      if (rd == 1)
+        rank_update<G, 1>(c, n, p.use_partial != 0);
+      else if (rd == 2)
+        rank_update<G, 2>(c, n, p.use_partial != 0);
+      else
+        rank_update<G, 3>(c, n, p.use_partial != 0);
+    } else if (c.tid == 0) {
+      c.sc[SC_FLAGS] |= VIEKF_FLAG_NAN_GAIN;
+      c.sc[SC_NNAN] += 1;
+    }
+    c.sync();
+  }
+  for (int i = c.tid; i < len; i += G) fix_depth_one(c, p, i);
+  c.sync();
+  return VIEKF_MEAS_SUCCESS;
+}
+
+// ------------------------------------------------------------------------------------------------------------------
+// STAT
+// ------------------------------------------------------------------------------------------------------------------
+template <int G>
+__device__ void ev_stat(Ctx<G>& c, const KParams& p, const viekf_event& E, int64_t ginst) {
+  if (!p.stats || E.id < 0 || E.id >= p.n_buckets) return;
+  c.sync();
+  double* er = c.sm + SM_ER;
+  double* out = c.sm + SM_HC;  // [2] NEES16, NEES6
+  if (c.tid == 0) {
+    double xt[17];
+    for (int i = 0; i < 8; i++) xt[i] = E.z[i];
+    for (int i = 0; i < 9; i++) xt[8 + i] = E.R[i];
+    if (E.noise >= 0 && p.values) {
+      const double* v = p.values + c.b * p.vstride + 8 * (int64_t)E.noise;
+      for (int i = 0; i < 6; i++) xt[10 + i] = v[i];
+    }
+    if (p.seed) {
+      double bi[6];
+      for (int k = 0; k < 6; k++) bi[k] = p.bias_range[k] * viekf_uniform_pm1(p.seed, (uint64_t)ginst, VIEKF_NOISE_EVENT_BIAS, k);
+      Q4 qbu = ldq(p.qbu);
+      V3 ba = rota(qbu, mk3(bi[0], bi[1], bi[2])), bg = rota(qbu, mk3(bi[3], bi[4], bi[5]));
+      xt[10] += ba.x; xt[11] += ba.y; xt[12] += ba.z;
+      xt[13] += bg.x; xt[14] += bg.y; xt[15] += bg.z;
+    }
+    const double* x = c.x;
+    for (int i = 0; i < 6; i++) er[i] = xt[i] - x[i];
+    V3 d = qboxminus(ldq(xt + 6), ldq(x + 6));
+    er[6] = d.x; er[7] = d.y; er[8] = d.z;
+    for (int i = 0; i < 7; i++) er[9 + i] = xt[10 + i] - x[10 + i];
+  }
+  c.sync();
+  // NEES by Cholesky of the 16x16 base block (thread 0) and of the 6x6 pose block (thread 1 or 0)
+  if (c.tid < 2 && (G > 1)) {
+    const int m = (c.tid == 0) ? 16 : 6;
+    const int pose[6] = {0, 1, 2, 6, 7, 8};
+    double L[136];
+    double y[16];
+    double qv = 0;
+    for (int i = 0; i < m; i++) {
+      const int ii = (c.tid == 0) ? i : pose[i];
+      for (int j = 0; j <= i; j++) {
+        const int jj = (c.tid == 0) ? j : pose[j];
+        double s = c.P[psym(ii, jj)];
+        for (int k = 0; k < j; k++) s -= L[plo(i, k)] * L[plo(j, k)];
+        L[plo(i, j)] = (i == j) ? sqrt(s) : s / L[plo(j, j)];
+      }
+      double s = er[ii];
+      for (int k = 0; k < i; k++) s -= L[plo(i, k)] * y[k];
+      y[i] = s / L[plo(i, i)];
+      qv += y[i] * y[i];
+    }
+    out[c.tid] = qv;
+  }
+  c.sync();
+  double* st = p.stats + (size_t)E.id * VIEKF_STAT_WIDTH;
+  for (int k = c.tid; k < 37; k += G) {
+    double v;
+    if (k == 0) v = 1.0;
+    else if (k <= 16) v = er[k - 1];
+    else if (k <= 32) v = er[k - 17] * er[k - 17];
+    else if (k == 33) v = out[0];
+    else if (k == 34) v = out[1];
+    else if (k == 35) v = (double)c.sc[SC_NGATED];
+    else v = (double)c.sc[SC_NFIX];
+    atomicAdd(st + k, v);
+  }
+  c.sync();
+}
+
+// ------------------------------------------------------------------------------------------------------------------
+// the persistent tape executor
+// ------------------------------------------------------------------------------------------------------------------
+template <int G>
+__global__ void __launch_bounds__((G >= 128 ? G : 128)) viekf_tape_kernel(const __grid_constant__ KParams p) {
+  extern __shared__ __align__(16) double smem[];
+  constexpr int CTA = (G >= 128 ? G : 128);
+  constexpr int GPC = CTA / G;
+  const Layout L = make_layout(p.N);
+  Ctx<G> c;
+  c.gi = threadIdx.x / G;
+  c.tid = threadIdx.x % G;
+  double* base = smem + (size_t)c.gi * L.total;
+  c.x = base + L.x; c.P = base + L.P; c.lam = base + L.lam; c.dx = base + L.dx; c.Abd = base + L.Abd; c.T = base + L.T;
+  c.Ac = base + L.Ac; c.Gb = base + L.Gb; c.Afd = base + L.Afd; c.Gd = base + L.Gd; c.Y = base + L.Y; c.upd = base + L.upd;
+  c.sm = base + L.small;
+  c.ids = (int*)(base + L.ids);
+  c.rm = c.ids + p.N;
+  c.sc = c.rm + p.N;
+  c.tcur = c.sm + SM_T;
+  const int nmax = 16 + 3 * p.N;
+  for (int i = c.tid; i < nmax; i += G) c.lam[i] = (i < 16) ? p.lam[i] : p.lamf[(i - 16) % 3];
+
+  for (int64_t b = (int64_t)blockIdx.x * GPC + c.gi; b < p.B; b += (int64_t)gridDim.x * GPC) {
+    c.b = b;
+    const int64_t ginst = p.inst_off + b;
+    FilterMeta& M = p.meta[b];
+    // ---- load the filter: meta, ids, live part of x and of the packed P ----
+    c.sync();
+    const int len0 = M.len;
+    if (c.tid == 0) {
+      c.sc[SC_LEN] = len0; c.sc[SC_NEXT] = M.next_id; c.sc[SC_STARTED] = M.started; c.sc[SC_FLAGS] = (int)M.flags;
+      c.sc[SC_NGATED] = (int)M.n_gated; c.sc[SC_NFIX] = (int)M.n_fix; c.sc[SC_NNAN] = (int)M.n_nan_gain; c.sc[SC_NKF] = M.n_kf;
+      *c.tcur = M.t;
+    }
+    for (int i = c.tid; i < len0; i += G) c.ids[i] = p.ids[b * (p.N > 0 ? p.N : 1) + i];
+    {
+      const double* gx = p.x + b * p.xs;
+      const int nx = 17 + 5 * len0;
+      for (int i = c.tid; i < nx; i += G) c.x[i] = gx[i];
+      const double2* gP = (const double2*)(p.P + b * p.ps);
+      double2* sP = (double2*)c.P;
+      const int n0 = 16 + 3 * len0;
+      const int np2 = (n0 * (n0 + 1) / 2 + 1) >> 1;
+      for (int i = c.tid; i < np2; i += G) sP[i] = gP[i];
+    }
+    c.sync();
+    // ---- run the tape slice ----
+    for (int64_t e = p.ev_first; e < p.ev_first + p.ev_count; e++) {
+      const viekf_event& E = p.ev[e];
+      const int kind = E.kind;
+      // resolve this instance's values for the event: shared z | per-instance block, plus generated noise
+      if (kind == VIEKF_EV_PROP || kind == VIEKF_EV_UPD || kind == VIEKF_EV_INIT) {
+        if (c.tid < 8) {
+          const int k = c.tid;
+          double v = (E.noise >= 0 && p.values) ? p.values[b * p.vstride + 8 * (int64_t)E.noise + k] : E.z[k];
+          if (p.seed) {
+            const double sg = E.sigma[k];
+            const double sgo = E.sigma[k ^ 1];
+            if (sg != 0.0 || sgo != 0.0) {
+              double nn[2];
+              viekf_normal_pair(p.seed, (uint64_t)ginst, (uint32_t)e, (uint32_t)(k >> 1), nn);
+              v += sg * nn[k & 1];
+            }
+            if (kind == VIEKF_EV_PROP && k < 6 && p.bias_range[k] != 0.0)
+              v += p.bias_range[k] * viekf_uniform_pm1(p.seed, (uint64_t)ginst, VIEKF_NOISE_EVENT_BIAS, k);
+          }
+          c.sm[SM_ZV + k] = v;
+        }
+        c.sync();
+      }
+      int result = VIEKF_MEAS_NONE;
+      switch (kind) {
+        case VIEKF_EV_PROP:
+          ev_propagate(c, p, E);
+          break;
+        case VIEKF_EV_UPD:
+          result = ev_update(c, p, E);
+          break;
+        case VIEKF_EV_INIT:
+          result = do_init_feature(c, p, c.sm[SM_ZV], c.sm[SM_ZV + 1], E.z[4]) ? 1 : 0;
+          break;
+        case VIEKF_EV_CLEAR:
+          do_clear_feature(c, p, find_feature(c, E.id));
+          break;
+        case VIEKF_EV_KEEP:
+          do_keep_only(c, p, p.id_pool + E.ids_off, E.n_ids);
+          break;
+        case VIEKF_EV_KFRESET:
+          do_keyframe_reset(c, p);
+          break;
+        case VIEKF_EV_STAT:
+          ev_stat(c, p, E, ginst);
+          break;
+        default:
+          break;
+      }
+      c.sync();
+      if (p.results && c.tid == 0 && b >= p.res_first && b < p.res_first + p.res_count)
+        p.results[(b - p.res_first) * p.n_events + e] = (uint8_t)result;
+    }
+    // ---- store the filter ----
+    c.sync();
+    const int len1 = c.sc[SC_LEN];
+    if (c.tid == 0) {
+      M.len = len1; M.next_id = c.sc[SC_NEXT]; M.started = c.sc[SC_STARTED]; M.flags = (uint32_t)c.sc[SC_FLAGS];
+      M.n_gated = (uint32_t)c.sc[SC_NGATED]; M.n_fix = (uint32_t)c.sc[SC_NFIX]; M.n_nan_gain = (uint32_t)c.sc[SC_NNAN]; M.n_kf = c.sc[SC_NKF];
+      M.t = *c.tcur;
+    }
+    for (int i = c.tid; i < len1; i += G) p.ids[b * (p.N > 0 ? p.N : 1) + i] = c.ids[i];
+    {
+      double* gx = p.x + b * p.xs;
+      const int nx = 17 + 5 * len1;
+      for (int i = c.tid; i < nx; i += G) gx[i] = c.x[i];
+      double2* gP = (double2*)(p.P + b * p.ps);
+      const double2* sP = (const double2*)c.P;
+      const int n1 = 16 + 3 * len1;
+      const int np2 = (n1 * (n1 + 1) / 2 + 1) >> 1;
+      for (int i = c.tid; i < np2; i += G) gP[i] = sP[i];
+    }
+  }
+}
+
+template <int G>
+static cudaError_t launch_g(const KParams& p, int sm_count, cudaStream_t stream) {
+  constexpr int CTA = (G >= 128 ? G : 128);
+  constexpr int GPC = CTA / G;
+  const size_t smem = smem_bytes_per_filter(p.N) * GPC;
+  cudaError_t e = cudaFuncSetAttribute(viekf_tape_kernel<G>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  if (e != cudaSuccess) return e;
+  int occ = 0;
+  e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, viekf_tape_kernel<G>, CTA, smem);
+  if (e != cudaSuccess) return e;
+  if (occ < 1) return cudaErrorInvalidConfiguration;
+  const int64_t need = (p.B + GPC - 1) / GPC;
+  int64_t grid = (int64_t)sm_count * occ;  // persistent: a whole number of waves of the SM count
+  if (need < grid) grid = need;
+  if (grid < 1) grid = 1;
+  viekf_tape_kernel<G><<<(unsigned)grid, CTA, smem, stream>>>(p);
+  return cudaGetLastError();
+}
+
+cudaError_t launch_tape(const KParams& p, int group, int sm_count, cudaStream_t stream) {
+  switch (group) {
+    case 32: return launch_g<32>(p, sm_count, stream);
+    case 64: return launch_g<64>(p, sm_count, stream);
+    case 128: return launch_g<128>(p, sm_count, stream);
+    case 256: return launch_g<256>(p, sm_count, stream);
+    default: return cudaErrorInvalidValue;
+  }
+}
+
+// ------------------------------------------------------------------------------------------------------------------
+// initialisation, read-out
+// ------------------------------------------------------------------------------------------------------------------
+__global__ void reset_kernel(const __grid_constant__ KParams p) {
+  const int64_t b = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (b >= p.B) return;
+  double* x = p.x + b * p.xs;
+  for (int i = 0; i < 17; i++) x[i] = p.x0[i];
+  double* P = p.P + b * p.ps;
+  for (int i = 0; i < 136; i++) P[i] = 0.0;
+  for (int i = 0; i < 16; i++) P[plo(i, i)] = p.P0[i];
+  FilterMeta m;
+  m.t = nan("");
+  for (int i = 0; i < 3; i++) m.node_t[i] = 0;
+  m.node_q[0] = 1; m.node_q[1] = m.node_q[2] = m.node_q[3] = 0;
+  for (int i = 0; i < 36; i++) m.gcov[i] = 0;
+  m.started = 0; m.len = 0; m.next_id = 0; m.n_kf = 0; m.flags = 0; m.n_gated = m.n_fix = m.n_nan_gain = 0;
+  p.meta[b] = m;
+}
+cudaError_t launch_reset(const KParams& p, cudaStream_t stream) {
+  reset_kernel<<<(unsigned)((p.B + 127) / 128), 128, 0, stream>>>(p);
+  return cudaGetLastError();
+}
+
+__global__ void set_x0_kernel(const __grid_constant__ KParams p, const double* x0, int broadcast) {
+  const int64_t b = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (b >= p.B) return;
+  const double* s = broadcast ? x0 : x0 + 17 * b;
+  double* x = p.x + b * p.xs;
+  for (int i = 0; i < 17; i++) x[i] = s[i];
+}
+cudaError_t launch_set_x0(const KParams& p, const double* x0_dev, int broadcast, cudaStream_t stream) {
+  set_x0_kernel<<<(unsigned)((p.B + 127) / 128), 128, 0, stream>>>(p, x0_dev, broadcast);
+  return cudaGetLastError();
+}
+
+// x <- x [+] (sqrt(P0) o n), n ~ N(0,1) from Philox(seed, global instance)
+__global__ void perturb_kernel(const __grid_constant__ KParams p, uint64_t seed) {
+  const int64_t b = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (b >= p.B) return;
+  double d[16];
+  for (int k = 0; k < 8; k++) {
+    double nn[2];
+    viekf_normal_pair(seed, (uint64_t)(p.inst_off + b), VIEKF_NOISE_EVENT_X0, k, nn);
+    d[2 * k] = sqrt(p.P0[2 * k]) * nn[0];
+    d[2 * k + 1] = sqrt(p.P0[2 * k + 1]) * nn[1];
+  }
+  double* x = p.x + b * p.xs;
+  for (int k = 0; k < 6; k++) x[k] += d[k];
+  stq(x + 6, otimes(ldq(x + 6), qexp(mk3(d[6], d[7], d[8]))));
+  for (int k = 0; k < 7; k++) x[10 + k] += d[9 + k];
+}
+cudaError_t launch_perturb(const KParams& p, uint64_t seed, cudaStream_t stream) {
+  perturb_kernel<<<(unsigned)((p.B + 127) / 128), 128, 0, stream>>>(p, seed);
+  return cudaGetLastError();
+}
+
+// get_state: [MAX_X x count], dead entries 0
+__global__ void unpack_state_kernel(const __grid_constant__ KParams p, int64_t first, int64_t count, double* out) {
+  const int mx = 17 + 5 * p.N;
+  const int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= count * mx) return;
+  const int64_t b = idx / mx;
+  const int i = (int)(idx - b * mx);
+  const int live = 17 + 5 * p.meta[first + b].len;
+  out[idx] = (i < live) ? p.x[(first + b) * p.xs + i] : 0.0;
+}
+cudaError_t launch_unpack_state(const KParams& p, int64_t first, int64_t count, double* o, cudaStream_t stream) {
+  const int64_t tot = count * (17 + 5 * p.N);
+  unpack_state_kernel<<<(unsigned)((tot + 255) / 256), 256, 0, stream>>>(p, first, count, o);
+  return cudaGetLastError();
+}
+
+// get_covariance: full symmetric [MAX_DX x MAX_DX x count] column-major, dead rows/cols 0
+__global__ void unpack_cov_kernel(const __grid_constant__ KParams p, int64_t first, int64_t count, double* out) {
+  const int n = 16 + 3 * p.N;
+  const int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= count * n * n) return;
+  const int64_t b = idx / ((int64_t)n * n);
+  const int r = (int)(idx - b * n * n);
+  const int j = r / n, i = r - j * n;
+  const int live = 16 + 3 * p.meta[first + b].len;
+  out[idx] = (i < live && j < live) ? p.P[(first + b) * p.ps + psym(i, j)] : 0.0;
+}
+cudaError_t launch_unpack_cov(const KParams& p, int64_t first, int64_t count, double* o, cudaStream_t stream) {
+  const int64_t n = 16 + 3 * p.N;
+  const int64_t tot = count * n * n;
+  unpack_cov_kernel<<<(unsigned)((tot + 255) / 256), 256, 0, stream>>>(p, first, count, o);
+  return cudaGetLastError();
+}
+
+// ------------------------------------------------------------------------------------------------------------------
+// FP64 FMA throughput probe (roofline denominator of the compute-bound kernels)
+// ------------------------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) dfma_probe_kernel(double* out, int iters, double a, double b) {
+  double r0 = threadIdx.x, r1 = r0 + 1, r2 = r0 + 2, r3 = r0 + 3, r4 = r0 + 4, r5 = r0 + 5, r6 = r0 + 6, r7 = r0 + 7;
+  for (int i = 0; i < iters; i++) {
+#pragma unroll
+    for (int u = 0; u < 8; u++) {
+      r0 = fma(r0, a, b); r1 = fma(r1, a, b); r2 = fma(r2, a, b); r3 = fma(r3, a, b);
+      r4 = fma(r4, a, b); r5 = fma(r5, a, b); r6 = fma(r6, a, b); r7 = fma(r7, a, b);
+    }
+  }
+  out[(size_t)blockIdx.x * blockDim.x + threadIdx.x] = ((r0 + r1) + (r2 + r3)) + ((r4 + r5) + (r6 + r7));
+}
+cudaError_t fp64_probe(int device, double* tflops) {
+  cudaError_t e = cudaSetDevice(device);
+  if (e != cudaSuccess) return e;
+  cudaDeviceProp prop;
+  e = cudaGetDeviceProperties(&prop, device);
+  if (e != cudaSuccess) return e;
+  const int blocks = prop.multiProcessorCount * 8, threads = 256, iters = 4096;
+  double* d = nullptr;
+  e = cudaMalloc(&d, sizeof(double) * blocks * threads);
+  if (e != cudaSuccess) return e;
+  cudaEvent_t e0, e1;
+  cudaEventCreate(&e0);
+  cudaEventCreate(&e1);
+  double best = 0;
+  for (int rep = 0; rep < 5; rep++) {
+    cudaEventRecord(e0);
+    dfma_probe_kernel<<<blocks, threads>>>(d, iters, 0.999999, 1e-9);
+    cudaEventRecord(e1);
+    e = cudaEventSynchronize(e1);
+    if (e != cudaSuccess) break;
+    float ms = 0;
+    cudaEventElapsedTime(&ms, e0, e1);
+    const double fl = 2.0 * 64.0 * (double)iters * blocks * threads;
+    const double tf = fl / (ms * 1e-3) / 1e12;
+    if (rep > 0 && tf > best) best = tf;
+  }
+  cudaEventDestroy(e0);
+  cudaEventDestroy(e1);
+  cudaFree(d);
+  *tflops = best;
+  return e;
+}
+
+}  // namespace vk

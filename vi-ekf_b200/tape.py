@@ -32,20 +32,26 @@ class TapeBuilder:
     def n_value_blocks(self):
         return self._n_value_blocks
 
-    def propagate(self, u, t, per_instance=False):
-        """propagate_state(u, t, save_input=False) (reference vi_ekf.cpp:262-318)."""
+    def propagate(self, u, t, per_instance=False, sigma=None):
+        """propagate_state(u, t, save_input=False) (reference vi_ekf.cpp:262-318).  sigma: per-instance white noise
+        std of the 6 IMU channels, drawn on the device when the tape is run with a seed."""
         e = self._new(abi.EV_PROP)
         e["t"] = t
         if u is not None:
             e["z"][:6] = u
+        if sigma is not None:
+            e["sigma"][:6] = sigma
         if per_instance:
             e["noise"] = self.value_block()
         return int(e["noise"])
 
-    def update(self, mtype, z, R, active=True, id=-1, depth=float("nan"), per_instance=False):
+    def update(self, mtype, z, R, active=True, id=-1, depth=float("nan"), per_instance=False, sigma=None):
         """add_measurement + update, in order (reference vi_ekf_meas.cpp:130-147,196-278)."""
         e = self._new(abi.EV_UPD)
         z = np.atleast_1d(np.asarray(z, dtype=np.float64))
+        if sigma is not None:
+            sg = np.atleast_1d(np.asarray(sigma, dtype=np.float64))
+            e["sigma"][: sg.size] = sg
         R = np.atleast_2d(np.asarray(R, dtype=np.float64))
         e["type"] = mtype
         e["zdim"] = z.size
