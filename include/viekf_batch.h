@@ -108,7 +108,10 @@ typedef struct viekf_event {
   int32_t n_ids;  /* KEEP: number of ids */
   int32_t ids_off;/* KEEP: offset into the tape's id pool */
   int32_t noise;  /* >=0: index of the per-instance value block for this event (see viekf_tape), -1: z is shared */
-  int32_t pad;
+  int32_t aux;    /* PROP: >= 0 = index of the physical IMU sample; all PROP events of one sample (an interval split by a
+                     measurement) then draw the same generated noise; -1 = key the noise by the event index.
+                     UPD: 1 = take z[k], k < zdim, from the body-frame IMU input of the filter's last propagate_state
+                     (the drag-accelerometer measurement of src/vi_ekf_ros.cpp:180-184), 0 = use z */
   double t;       /* PROP: absolute time of the IMU sample; others: informational */
   double z[8];    /* PROP: u = [acc(3), gyro(3)] in the IMU frame; UPD: z[0..zdim), z[4] = depth (FEAT);
                      INIT: pixel(2), z[4] = depth (NaN = unknown); STAT: true pos(3) vel(3) att(4)=10 -> see truth block */

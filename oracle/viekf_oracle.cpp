@@ -314,6 +314,7 @@ void VIEKF::propagate_state(const double u[6], double t, bool save_input) {
     ub[i] = a[i];
     ub[3 + i] = g[i];
   }
+  for (int i = 0; i < 6; i++) ub_last_[i] = ub[i];
   if (save_input) {
     std::array<double, 6> s;
     for (int i = 0; i < 6; i++) s[i] = ub[i];
@@ -912,7 +913,8 @@ void VIEKF::run_tape(const viekf_event* ev, int64_t n, const int32_t* id_pool, c
       for (int k = 0; k < 8; k += 2)
         if (E.sigma[k] != 0.0 || E.sigma[k + 1] != 0.0) {
           double nn[2];
-          viekf_normal_pair(seed, ginst, (uint32_t)e, (uint32_t)(k >> 1), nn);
+          const uint32_t key = (E.kind == VIEKF_EV_PROP && E.aux >= 0) ? (0x80000000u | (uint32_t)E.aux) : (uint32_t)e;
+          viekf_normal_pair(seed, ginst, key, (uint32_t)(k >> 1), nn);
           zbuf[k] += E.sigma[k] * nn[0];
           zbuf[k + 1] += E.sigma[k + 1] * nn[1];
         }
@@ -928,7 +930,7 @@ void VIEKF::run_tape(const viekf_event* ev, int64_t n, const int32_t* id_pool, c
         break;
       case VIEKF_EV_UPD: {
         double z[4] = {0, 0, 0, 0};
-        for (int i = 0; i < E.zdim; i++) z[i] = zv[i];
+        for (int i = 0; i < E.zdim; i++) z[i] = (E.aux == 1) ? ub_last_[i] : zv[i];
         res = update_direct(E.type, z, E.zdim, E.R, E.rdim, E.active != 0, E.id, E.z[4]);
         break;
       }

@@ -329,6 +329,7 @@ class VIEKF {
   std::vector<double> dx_;
   Mat H_, K_;
   double zhat_[4];
+  double ub_last_[6] = {0, 0, 0, 0, 0, 0};  // body-frame IMU input of the last propagate_state call
   uint32_t flags = 0;
   uint32_t n_gated = 0, n_fix = 0, n_nan_gain = 0;
   double min_gate_margin = 1e300;  // min |mahal - 9| seen (SURVEY 7 "hard parts": reject seeds with tiny margins)

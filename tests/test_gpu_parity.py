@@ -56,7 +56,7 @@ def test_tape_parity_all_event_kinds(pkg, oracle_mod, NF, steps):
     _compare(bk, ref, tag=f"N={NF}")
     st = bk.stats(nb)
     assert np.allclose(st[:, 0], B)
-    assert np.allclose(st, ref["stats"], rtol=1e-7, atol=1e-9)
+    assert np.allclose(st, ref["stats"], rtol=1e-7, atol=1e-9, equal_nan=True)
     if NF > 0:
         pose, gcov = bk.get_global_pose()
         t7, c36 = f.global_pose()
@@ -109,7 +109,7 @@ def test_per_instance_values(pkg, oracle_mod):
     assert np.array_equal(res, ref["results"])
     assert len({tuple(r) for r in res}) > 1, "perturbed instances should not all take the same decisions"
     _compare(bk, ref, tag="values")
-    assert np.allclose(bk.stats(nb), ref["stats"], rtol=1e-7, atol=1e-9)
+    assert np.allclose(bk.stats(nb), ref["stats"], rtol=1e-7, atol=1e-9, equal_nan=True)
 
 
 def test_generated_noise_and_sharding(pkg, oracle_mod):
@@ -132,7 +132,7 @@ def test_generated_noise_and_sharding(pkg, oracle_mod):
     res = bk.run_tape(ev, idp, results_first=0, results_count=B, seed=seed, bias_range=bias)
     assert np.array_equal(res, ref["results"])
     _compare(bk, ref, tag="noise")
-    assert np.allclose(bk.stats(nb), ref["stats"], rtol=1e-7, atol=1e-9)
+    assert np.allclose(bk.stats(nb), ref["stats"], rtol=1e-7, atol=1e-9, equal_nan=True)
     xa, Pa = bk.get_state(), bk.get_covariance()
     h = B // 2
     parts = []
@@ -301,7 +301,7 @@ def test_thousand_steps_25_features(pkg, oracle_mod):
     assert np.array_equal(res, ref["results"])
     worst = _compare(bk, ref, tag="1000 steps N=25")
     print(f"1000 steps, N=25: worst state rel err {worst[0]:.2e}, covariance rel err {worst[1]:.2e}")
-    assert np.allclose(bk.stats(nb), ref["stats"], rtol=1e-6, atol=1e-9)
+    assert np.allclose(bk.stats(nb), ref["stats"], rtol=1e-6, atol=1e-9, equal_nan=True)
 
 
 @pytest.mark.parametrize("B,NF,steps", [(65536, 0, 50), (65536, 8, 14), (262144, 25, 8)])

@@ -72,7 +72,7 @@ def default_config():
 # numpy mirror of viekf_event (248 bytes)
 EVENT_DTYPE = np.dtype([
     ("kind", "<i4"), ("type", "<i4"), ("id", "<i4"), ("active", "<i4"), ("zdim", "<i4"), ("rdim", "<i4"),
-    ("n_ids", "<i4"), ("ids_off", "<i4"), ("noise", "<i4"), ("pad", "<i4"),
+    ("n_ids", "<i4"), ("ids_off", "<i4"), ("noise", "<i4"), ("aux", "<i4"),
     ("t", "<f8"), ("z", "<f8", (8,)), ("R", "<f8", (9,)), ("sigma", "<f8", (8,)),
 ], align=True)
 assert EVENT_DTYPE.itemsize == 248

@@ -14,6 +14,7 @@ struct FilterMeta {
   double node_t[3];  // current_node_global_pose_.t
   double node_q[4];  // current_node_global_pose_.q
   double gcov[36];   // global_pose_cov_ (column-major 6x6)
+  double ub[6];      // body-frame IMU input of the last propagate_state call
   int32_t started;   // !isnan(start_t_)
   int32_t len;       // len_features_
   int32_t next_id;   // next_feature_id_

@@ -50,7 +50,7 @@ __host__ __device__ inline Layout make_layout(int N) {
   L.upd = L.Afd;                      // update workspace (PHt, K, KS: 9 n) overlays the propagate workspace
   const int upd_end = L.upd + ev2(9 * nmax);
   if (upd_end > o) o = upd_end;
-  L.small = o; o += 64;
+  L.small = o; o += 80;
   L.ids = o;   o += ev2(N + 12);  // ids[N] + rm[N] + scalars[SC_COUNT + 9], as int32
   L.total = ev2(o);
   return L;
@@ -73,7 +73,7 @@ template <int G>
 struct Ctx {
   double *x, *P, *lam, *dx, *Abd, *T, *Ac, *Gb, *Afd, *Gd, *Y, *upd, *sm;
   int *ids, *rm, *sc;
-  double* tcur;  // filter time lives in sm[63]
+  double* tcur;  // filter time lives in sm[SM_T]
   int tid, gi;
   int64_t b;
   __device__ __forceinline__ void sync() const {
@@ -84,8 +84,8 @@ struct Ctx {
   }
 };
 
-// small scratch slots inside sm[64]
-enum { SM_ZV = 0 /*8*/, SM_HC = 8 /*18*/, SM_S = 26 /*9*/, SM_SI = 35 /*9*/, SM_RES = 44 /*4*/, SM_ER = 44 /*16, STAT only*/, SM_T = 63 };
+// small scratch slots inside sm[80]
+enum { SM_ZV = 0 /*8*/, SM_HC = 8 /*18*/, SM_S = 26 /*9*/, SM_SI = 35 /*9*/, SM_RES = 44 /*4*/, SM_ER = 48 /*16*/, SM_UB = 64 /*6*/, SM_T = 70 };
 
 // ------------------------------------------------------------------------------------------------------------------
 // PROP
@@ -275,6 +275,14 @@ __device__ __forceinline__ void boxplus_inplace(const Ctx<G>& c, const double* d
 
 template <int G>
 __device__ void ev_propagate(Ctx<G>& c, const KParams& p, const viekf_event& E) {
+  // the body-frame input of the latest propagate_state call is kept for UPD events with aux == 1 (vi_ekf.cpp:265-267)
+  if (c.tid == 0) {
+    const double* zz = c.sm + SM_ZV;
+    Q4 qbu = ldq(p.qbu);
+    V3 a = rota(qbu, mk3(zz[0], zz[1], zz[2])), g = rota(qbu, mk3(zz[3], zz[4], zz[5]));
+    double* ul = c.sm + SM_UB;
+    ul[0] = a.x; ul[1] = a.y; ul[2] = a.z; ul[3] = g.x; ul[4] = g.y; ul[5] = g.z;
+  }
   // uniform control flow: every thread evaluates the same guards from shared state (vi_ekf.cpp:274-289)
   const int started = c.sc[SC_STARTED];
   const double tcur = *c.tcur;
@@ -288,7 +296,10 @@ __device__ void ev_propagate(Ctx<G>& c, const KParams& p, const viekf_event& E) 
     c.sync();
     return;
   }
-  if (fabs(dt) < 1e-6) return;
+  if (fabs(dt) < 1e-6) {
+    c.sync();
+    return;
+  }
   if (dt < 0) {
     if (c.tid == 0) c.sc[SC_FLAGS] |= VIEKF_FLAG_BACKWARD_DT;
     c.sync();
@@ -1093,6 +1104,7 @@ __global__ void __launch_bounds__((G >= 128 ? G : 128)) viekf_tape_kernel(const 
       c.sc[SC_LEN] = len0; c.sc[SC_NEXT] = M.next_id; c.sc[SC_STARTED] = M.started; c.sc[SC_FLAGS] = (int)M.flags;
       c.sc[SC_NGATED] = (int)M.n_gated; c.sc[SC_NFIX] = (int)M.n_fix; c.sc[SC_NNAN] = (int)M.n_nan_gain; c.sc[SC_NKF] = M.n_kf;
       *c.tcur = M.t;
+      for (int k = 0; k < 6; k++) c.sm[SM_UB + k] = M.ub[k];
     }
     for (int i = c.tid; i < len0; i += G) c.ids[i] = p.ids[b * (p.N > 0 ? p.N : 1) + i];
     {
@@ -1120,12 +1132,14 @@ __global__ void __launch_bounds__((G >= 128 ? G : 128)) viekf_tape_kernel(const 
             const double sgo = E.sigma[k ^ 1];
             if (sg != 0.0 || sgo != 0.0) {
               double nn[2];
-              viekf_normal_pair(p.seed, (uint64_t)ginst, (uint32_t)e, (uint32_t)(k >> 1), nn);
+              const uint32_t key = (kind == VIEKF_EV_PROP && E.aux >= 0) ? (0x80000000u | (uint32_t)E.aux) : (uint32_t)e;
+              viekf_normal_pair(p.seed, (uint64_t)ginst, key, (uint32_t)(k >> 1), nn);
               v += sg * nn[k & 1];
             }
             if (kind == VIEKF_EV_PROP && k < 6 && p.bias_range[k] != 0.0)
               v += p.bias_range[k] * viekf_uniform_pm1(p.seed, (uint64_t)ginst, VIEKF_NOISE_EVENT_BIAS, k);
           }
+          if (kind == VIEKF_EV_UPD && E.aux == 1 && k < 6) v = c.sm[SM_UB + k];
           c.sm[SM_ZV + k] = v;
         }
         c.sync();
@@ -1167,6 +1181,7 @@ __global__ void __launch_bounds__((G >= 128 ? G : 128)) viekf_tape_kernel(const 
       M.len = len1; M.next_id = c.sc[SC_NEXT]; M.started = c.sc[SC_STARTED]; M.flags = (uint32_t)c.sc[SC_FLAGS];
       M.n_gated = (uint32_t)c.sc[SC_NGATED]; M.n_fix = (uint32_t)c.sc[SC_NFIX]; M.n_nan_gain = (uint32_t)c.sc[SC_NNAN]; M.n_kf = c.sc[SC_NKF];
       M.t = *c.tcur;
+      for (int k = 0; k < 6; k++) M.ub[k] = c.sm[SM_UB + k];
     }
     for (int i = c.tid; i < len1; i += G) p.ids[b * (p.N > 0 ? p.N : 1) + i] = c.ids[i];
     {
@@ -1227,6 +1242,7 @@ __global__ void reset_kernel(const __grid_constant__ KParams p) {
   for (int i = 0; i < 3; i++) m.node_t[i] = 0;
   m.node_q[0] = 1; m.node_q[1] = m.node_q[2] = m.node_q[3] = 0;
   for (int i = 0; i < 36; i++) m.gcov[i] = 0;
+  for (int i = 0; i < 6; i++) m.ub[i] = 0;
   m.started = 0; m.len = 0; m.next_id = 0; m.n_kf = 0; m.flags = 0; m.n_gated = m.n_fix = m.n_nan_gain = 0;
   p.meta[b] = m;
 }

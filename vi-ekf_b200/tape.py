@@ -32,11 +32,12 @@ class TapeBuilder:
     def n_value_blocks(self):
         return self._n_value_blocks
 
-    def propagate(self, u, t, per_instance=False, sigma=None):
+    def propagate(self, u, t, per_instance=False, sigma=None, sample=-1):
         """propagate_state(u, t, save_input=False) (reference vi_ekf.cpp:262-318).  sigma: per-instance white noise
         std of the 6 IMU channels, drawn on the device when the tape is run with a seed."""
         e = self._new(abi.EV_PROP)
         e["t"] = t
+        e["aux"] = sample
         if u is not None:
             e["z"][:6] = u
         if sigma is not None:
@@ -45,7 +46,7 @@ class TapeBuilder:
             e["noise"] = self.value_block()
         return int(e["noise"])
 
-    def update(self, mtype, z, R, active=True, id=-1, depth=float("nan"), per_instance=False, sigma=None):
+    def update(self, mtype, z, R, active=True, id=-1, depth=float("nan"), per_instance=False, sigma=None, from_imu=False):
         """add_measurement + update, in order (reference vi_ekf_meas.cpp:130-147,196-278)."""
         e = self._new(abi.EV_UPD)
         z = np.atleast_1d(np.asarray(z, dtype=np.float64))
@@ -61,6 +62,7 @@ class TapeBuilder:
         e["R"][: R.size] = R.T.ravel()  # column-major
         e["active"] = int(active)
         e["id"] = id
+        e["aux"] = 1 if from_imu else 0
         if per_instance:
             e["noise"] = self.value_block()
         return int(e["noise"])
