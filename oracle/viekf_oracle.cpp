@@ -976,16 +976,22 @@ void VIEKF::run_tape(const viekf_event* ev, int64_t n, const int32_t* id_pool, c
         }
         // NEES via Cholesky of the base block (16) and of the pose block (pos+att, 6)
         auto nees = [&](const int* idx, int m) {
+          // NEES is defined only for a positive-definite block: a non-positive pivot (the position block is exactly
+          // zero right after a keyframe reset) makes it NaN
           double L[16 * 16], y[16];
           const Mat& P = P_[i_];
-          for (int i = 0; i < m; i++)
+          double q = 0;
+          for (int i = 0; i < m; i++) {
             for (int j = 0; j <= i; j++) {
               double sum = P(idx[i], idx[j]);
               for (int k = 0; k < j; k++) sum -= L[i * 16 + k] * L[j * 16 + k];
-              L[i * 16 + j] = (i == j) ? std::sqrt(sum) : sum / L[j * 16 + j];
+              if (i == j) {
+                if (!(sum > 0.0)) return (double)NAN;
+                L[i * 16 + j] = std::sqrt(sum);
+              } else {
+                L[i * 16 + j] = sum / L[j * 16 + j];
+              }
             }
-          double q = 0;
-          for (int i = 0; i < m; i++) {
             double sum = er[idx[i]];
             for (int k = 0; k < i; k++) sum -= L[i * 16 + k] * y[k];
             y[i] = sum / L[i * 16 + i];

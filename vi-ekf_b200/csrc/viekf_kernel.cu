@@ -706,10 +706,11 @@ __device__ void do_keep_only(Ctx<G>& c, const KParams& p, const int32_t* feats, 
   c.sync();
   const int nrm = c.sc[SC_TMP0];
   const int overlap = c.sc[SC_TMP1];
-  for (int k = 0; k < nrm; k++) do_clear_feature(c, p, find_feature(c, c.rm[k]));
   const int nkf = c.sc[SC_NKF];
+  for (int k = 0; k < nrm; k++) do_clear_feature(c, p, find_feature(c, c.rm[k]));
   const bool reset = p.use_kfreset && nkf > 0 && ((double)overlap / (double)nkf < p.kf_thresh);
   if (reset) do_keyframe_reset(c, p);
+  c.sync();  // every thread has taken the (uniform) reset decision from the old list size before thread 0 replaces it
   if (p.use_kfreset && (reset || nkf == 0)) {
     int32_t* kf = p.kf_ids + c.b * KF_CAP;
     const int m = nf < KF_CAP ? nf : KF_CAP;
@@ -1039,20 +1040,27 @@ __device__ void ev_stat(Ctx<G>& c, const KParams& p, const viekf_event& E, int64
     double L[136];
     double y[16];
     double qv = 0;
+    bool bad = false;
     for (int i = 0; i < m; i++) {
       const int ii = (c.tid == 0) ? i : pose[i];
       for (int j = 0; j <= i; j++) {
         const int jj = (c.tid == 0) ? j : pose[j];
         double s = c.P[psym(ii, jj)];
         for (int k = 0; k < j; k++) s -= L[plo(i, k)] * L[plo(j, k)];
-        L[plo(i, j)] = (i == j) ? sqrt(s) : s / L[plo(j, j)];
+        if (i == j) {
+          if (!(s > 0.0)) bad = true;  // not positive definite (e.g. right after a keyframe reset): NEES undefined
+          L[plo(i, j)] = sqrt(s);
+        } else {
+          L[plo(i, j)] = s / L[plo(j, j)];
+        }
       }
+      if (bad) break;
       double s = er[ii];
       for (int k = 0; k < i; k++) s -= L[plo(i, k)] * y[k];
       y[i] = s / L[plo(i, i)];
       qv += y[i] * y[i];
     }
-    out[c.tid] = qv;
+    out[c.tid] = bad ? nan("") : qv;
   }
   c.sync();
   double* st = p.stats + (size_t)E.id * VIEKF_STAT_WIDTH;

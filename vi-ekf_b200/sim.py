@@ -313,9 +313,12 @@ def flops_update(n, r):
 
 
 def tape_flops(events, live, first=0, count=None):
-    """Algorithmic FP64 flops one filter spends on events[first:first+count] (every update counted as applied)."""
+    """Algorithmic FP64 flops one filter spends on events[first:first+count] (every update counted as applied):
+    returns (propagate flops, update flops, number of active updates)."""
     count = len(events) - first if count is None else count
     tot = 0.0
+    totu = 0.0
+    nupd = 0
     started = first > 0
     for i in range(first, first + count):
         e = events[i]
@@ -327,8 +330,9 @@ def tape_flops(events, live, first=0, count=None):
         elif e["kind"] == abi.EV_UPD:
             if e["type"] == abi.FEAT and i > 0 and live[i] != live[i - 1]:
                 continue  # initialisation of a new feature, no update
-            tot += flops_update(16 + 3 * nf, int(e["rdim"]))
-    return tot
+            totu += flops_update(16 + 3 * nf, int(e["rdim"]))
+            nupd += 1
+    return tot, totu, nupd
 
 
 def hbm_bytes_per_launch(nfeat):
