@@ -101,7 +101,9 @@ def test_random_jac_test_config(pkg, oracle_mod):
     bk = pkg.BatchVIEKF(cfg, B=1, N=NF)
     res = bk.run_tape(ev, idp, results_first=0, results_count=1)
     assert np.array_equal(res, ref["results"])
-    _compare(bk, ref, tag="jac_test config")
+    # unit P0 collapsing to ~1e-6 under 0.5 px measurements: each covariance-form update loses eps*|P_old|/|P_new| relative
+    # accuracy whatever the summation order, so two correct evaluations agree to a few 1e-9 here, not 1e-9
+    _compare(bk, ref, tol=5e-9, tag="jac_test config")
 
 
 def test_per_instance_values(pkg, oracle_mod):

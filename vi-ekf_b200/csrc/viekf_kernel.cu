@@ -29,7 +29,7 @@ namespace vk {
 // shared-memory layout of one filter (offsets in doubles), a function of N only
 // ------------------------------------------------------------------------------------------------------------------
 struct Layout {
-  int x, P, lam, dx, Abd, T, Ac, Gb, Afd, Gd, Y, upd, small, ids, total;
+  int x, P, lam, dx, Abd, AbT, T, Ac, Gb, Afd, Gd, Y, upd, small, ids, total;
 };
 __host__ __device__ inline int ev2(int v) { return (v + 1) & ~1; }
 __host__ __device__ inline Layout make_layout(int N) {
@@ -41,14 +41,15 @@ __host__ __device__ inline Layout make_layout(int N) {
   L.lam = o;   o += ev2(nmax);
   L.dx = o;    o += ev2(nmax);
   L.Abd = o;   o += 256;
+  L.AbT = o;   o += 256;  // A_bb transposed (bank-conflict-free column access in P'_fb = Y A_bb^T)
   L.T = o;     o += 256;
   L.Ac = o;    o += 144;
   L.Gb = o;    o += 54 + 2;
   L.Afd = o;   o += ev2(3 * N * 19);
   L.Gd = o;    o += ev2(nmax * 6);
   L.Y = o;     o += ev2(3 * N * 16);  // also the continuous feature blocks (27 per feature) before discretisation
-  L.upd = L.Afd;                      // update workspace (PHt, K, KS: 9 n) overlays the propagate workspace
-  const int upd_end = L.upd + ev2(9 * nmax);
+  L.upd = L.Afd;                      // update workspace (P H^T, K, K S, 1-lambda: 10 n) overlays the propagate workspace
+  const int upd_end = L.upd + ev2(10 * nmax);
   if (upd_end > o) o = upd_end;
   L.small = o; o += 80;
   L.ids = o;   o += ev2(N + 12);  // ids[N] + rm[N] + scalars[SC_COUNT + 9], as int32
@@ -61,8 +62,7 @@ size_t smem_bytes_per_filter(int N) { return (size_t)make_layout(N).total * size
 int group_size_for(int N) {
   if (N <= 1) return 32;
   if (N <= 6) return 64;
-  if (N <= 16) return 128;
-  return 256;
+  return 128;
 }
 
 // scalars kept as int32 behind the ids array
@@ -71,9 +71,10 @@ enum { SC_LEN = 0, SC_NEXT = 1, SC_STARTED = 2, SC_FLAGS = 3, SC_NGATED = 4, SC_
 
 template <int G>
 struct Ctx {
-  double *x, *P, *lam, *dx, *Abd, *T, *Ac, *Gb, *Afd, *Gd, *Y, *upd, *sm;
+  double *x, *P, *lam, *dx, *Abd, *AbT, *T, *Ac, *Gb, *Afd, *Gd, *Y, *upd, *sm;
   int *ids, *rm, *sc;
   double* tcur;  // filter time lives in sm[SM_T]
+  const double* zv;  // this event's resolved per-instance values (one of the two SM_ZV buffers)
   int tid, gi;
   int64_t b;
   __device__ __forceinline__ void sync() const {
@@ -85,7 +86,7 @@ struct Ctx {
 };
 
 // small scratch slots inside sm[80]
-enum { SM_ZV = 0 /*8*/, SM_HC = 8 /*18*/, SM_S = 26 /*9*/, SM_SI = 35 /*9*/, SM_RES = 44 /*4*/, SM_ER = 48 /*16*/, SM_UB = 64 /*6*/, SM_T = 70 };
+enum { SM_ZV = 0 /*2 x 8, double buffered*/, SM_HC = 16 /*18*/, SM_RES = 34 /*4*/, SM_ER = 38 /*16*/, SM_UB = 54 /*6*/, SM_T = 60 };
 
 // ------------------------------------------------------------------------------------------------------------------
 // PROP
@@ -277,7 +278,7 @@ template <int G>
 __device__ void ev_propagate(Ctx<G>& c, const KParams& p, const viekf_event& E) {
   // the body-frame input of the latest propagate_state call is kept for UPD events with aux == 1 (vi_ekf.cpp:265-267)
   if (c.tid == 0) {
-    const double* zz = c.sm + SM_ZV;
+    const double* zz = c.zv;
     Q4 qbu = ldq(p.qbu);
     V3 a = rota(qbu, mk3(zz[0], zz[1], zz[2])), g = rota(qbu, mk3(zz[3], zz[4], zz[5]));
     double* ul = c.sm + SM_UB;
@@ -307,7 +308,7 @@ __device__ void ev_propagate(Ctx<G>& c, const KParams& p, const viekf_event& E) 
   }
   const int len = c.sc[SC_LEN];
   const int n = 16 + 3 * len;
-  const double* zv = c.sm + SM_ZV;
+  const double* zv = c.zv;
   // IMU sample into the body frame (vi_ekf.cpp:265-267)
   double ub[6];
   {
@@ -327,7 +328,10 @@ __device__ void ev_propagate(Ctx<G>& c, const KParams& p, const viekf_event& E) 
       double* Ad = c.Abd + r * 16;
       double* Gd = c.Gd + r * 6;
       if (r >= 9) {
-        for (int k = 0; k < 16; k++) Ad[k] = (k == r) ? 1.0 : 0.0;
+        for (int k = 0; k < 16; k++) {
+          Ad[k] = (k == r) ? 1.0 : 0.0;
+          c.AbT[k * 16 + r] = Ad[k];
+        }
         for (int q = 0; q < 6; q++) Gd[q] = 0.0;
       } else {
         const double* Ar = c.Ac + r * 16;
@@ -337,6 +341,7 @@ __device__ void ev_propagate(Ctx<G>& c, const KParams& p, const viekf_event& E) 
           for (int k = 3; k < 9; k++) aa += Ar[k] * c.Ac[k * 16 + cc];
           const double id = (cc == r) ? 1.0 : 0.0;
           Ad[cc] = (id + Ar[cc] * dt) + aa * h2;
+          c.AbT[cc * 16 + r] = Ad[cc];
           if (cc < 9) m[cc] = (id + Ar[cc] * hd2) + aa * h6;
         }
         for (int q = 0; q < 6; q++) {
@@ -476,7 +481,7 @@ __device__ void ev_propagate(Ctx<G>& c, const KParams& p, const viekf_event& E) 
     const int fr = task >> 4, cc = task & 15;
     double s = 0;
 #pragma unroll
-    for (int k = 0; k < 16; k++) s += c.Y[fr * 16 + k] * c.Abd[cc * 16 + k];
+    for (int k = 0; k < 16; k++) s += c.Y[fr * 16 + k] * c.AbT[k * 16 + cc];
 #pragma unroll
     for (int q = 0; q < 6; q++) s += (c.Gd[(16 + fr) * 6 + q] * p.Qu[q]) * c.Gd[cc * 6 + q];
     c.P[plo(16 + fr, cc)] = s;
@@ -723,53 +728,243 @@ __device__ void do_keep_only(Ctx<G>& c, const KParams& p, const int32_t* feats, 
 // ------------------------------------------------------------------------------------------------------------------
 // UPD
 // ------------------------------------------------------------------------------------------------------------------
-// symmetric rank update of the packed P:  P_ij += L_ij * ( KS_i.K_j - K_i.H_j - H_i.K_j ),  H = (HP)^T = P H^T
+// symmetric rank update of the packed P:
+//   P_ij += (1 - a_i a_j) * ( KS_i.K_j - K_i.H_j - H_i.K_j ),   H = (HP)^T = P H^T,   a = 1 - lambda (partial update) or 0
+// Work item = 4 rows x all 32-column chunks of that row block; the row vectors are loaded once per row block
+// (broadcast), the column vectors once per chunk (16-byte vector loads, conflict free), P is read and written once.
+// Vectors live in the update workspace: Kv/Hv/KSv hold components 0,1 as double2, K2/H2/KS2 component 2 (RD == 3).
+template <int G>
+struct UpdVec {
+  double2 *Kv, *Hv, *KSv;
+  double *K2, *H2, *KS2, *av;
+  __device__ __forceinline__ UpdVec(const Ctx<G>& c, int nmax) {
+    double* w = c.upd;
+    Kv = (double2*)w;
+    Hv = (double2*)(w + 2 * nmax);
+    KSv = (double2*)(w + 4 * nmax);
+    K2 = w + 6 * nmax;
+    H2 = w + 7 * nmax;
+    KS2 = w + 8 * nmax;
+    av = w + 9 * nmax;
+  }
+};
+
 template <int G, int RD>
-__device__ __forceinline__ void rank_update(const Ctx<G>& c, int n, bool partial) {
-  const double* PHt = c.upd;
-  const double* K = c.upd + 3 * n;
-  const double* KS = c.upd + 6 * n;
+__device__ __forceinline__ void rank_update(const Ctx<G>& c, const UpdVec<G>& v, int n) {
   const int lane = c.tid & 31, warp = c.tid >> 5;
   constexpr int NW = G / 32;
   constexpr int RB = 4;
-  int item = 0;
-  for (int i0 = 0; i0 < n; i0 += RB) {
-    const int cmax = min(i0 + RB, n);
-    for (int j0 = 0; j0 < cmax; j0 += 32, item++) {
-      if ((item % NW) != warp) continue;
-      const int j = j0 + lane;
-      if (j >= cmax) continue;
-      double kj[RD], hj[RD];
+  const int nrb = (n + RB - 1) / RB;
+  for (int rb = warp; rb < nrb; rb += NW) {
+    const int i0 = rb * RB;
+    double2 ki[RB], hi[RB], si[RB];
+    double k2[RB], h2[RB], s2[RB], ai[RB];
 #pragma unroll
-      for (int a = 0; a < RD; a++) {
-        kj[a] = K[j * 3 + a];
-        hj[a] = PHt[j * 3 + a];
+    for (int r = 0; r < RB; r++) {
+      const int i = min(i0 + r, n - 1);
+      ki[r] = v.Kv[i];
+      hi[r] = v.Hv[i];
+      si[r] = v.KSv[i];
+      ai[r] = v.av[i];
+      if (RD == 3) {
+        k2[r] = v.K2[i];
+        h2[r] = v.H2[i];
+        s2[r] = v.KS2[i];
       }
-      const double lj = c.lam[j];
+    }
+    const int cmax = min(i0 + RB, n);
+    for (int j = lane; j < cmax; j += 32) {
+      const double2 kj = v.Kv[j], hj = v.Hv[j];
+      const double aj = v.av[j];
+      double kj2 = 0, hj2 = 0;
+      if (RD == 3) {
+        kj2 = v.K2[j];
+        hj2 = v.H2[j];
+      }
+      double* Pc = c.P + plo(i0, j);
+      int off = 0;
 #pragma unroll
       for (int r = 0; r < RB; r++) {
         const int i = i0 + r;
         if (i < n && j <= i) {
-          double d = 0;
-#pragma unroll
-          for (int a = 0; a < RD; a++) d += KS[i * 3 + a] * kj[a] - K[i * 3 + a] * hj[a] - PHt[i * 3 + a] * kj[a];
-          const int e = plo(i, j);
-          if (partial) {
-            const double li = c.lam[i];
-            c.P[e] += ((lj + li) - li * lj) * d;
-          } else {
-            c.P[e] += d;
+          double d = si[r].x * kj.x;
+          d = fma(-ki[r].x, hj.x, d);
+          d = fma(-hi[r].x, kj.x, d);
+          if (RD >= 2) {
+            d = fma(si[r].y, kj.y, d);
+            d = fma(-ki[r].y, hj.y, d);
+            d = fma(-hi[r].y, kj.y, d);
           }
+          if (RD == 3) {
+            d = fma(s2[r], kj2, d);
+            d = fma(-k2[r], hj2, d);
+            d = fma(-h2[r], kj2, d);
+          }
+          const double u = fma(-ai[r], aj, 1.0);
+          Pc[off] = fma(d, u, Pc[off]);
         }
+        off += i + 1;  // next packed row starts i+1 further
       }
     }
   }
 }
 
+// S^-1 by partial-pivot LU on an RD x RD system held in registers (what Eigen's dynamic-size inverse() does,
+// vi_ekf_meas.cpp:232; same operation order as the oracle's small_inverse), and the Mahalanobis distance.
+template <int RD>
+__device__ __forceinline__ double inverse_and_mahal(const double (&S)[3][3], double (&Si)[3][3], const double* res) {
+  double a[RD][2 * RD];
+#pragma unroll
+  for (int i = 0; i < RD; i++)
+#pragma unroll
+    for (int j = 0; j < RD; j++) {
+      a[i][j] = S[i][j];
+      a[i][j + RD] = (i == j) ? 1.0 : 0.0;
+    }
+#pragma unroll
+  for (int cc = 0; cc < RD; cc++) {
+    // partial pivoting: `if (|a[i][cc]| > |a[pv][cc]|) pv = i`, rows swapped by value so every index stays static
+    int pv = cc;
+    double apv = fabs(a[cc][cc]);
+#pragma unroll
+    for (int i = cc + 1; i < RD; i++) {
+      const double ai = fabs(a[i][cc]);
+      if (ai > apv) {
+        pv = i;
+        apv = ai;
+      }
+    }
+#pragma unroll
+    for (int i = cc + 1; i < RD; i++)
+      if (pv == i) {
+#pragma unroll
+        for (int j = 0; j < 2 * RD; j++) {
+          const double t = a[cc][j];
+          a[cc][j] = a[i][j];
+          a[i][j] = t;
+        }
+      }
+#pragma unroll
+    for (int i = cc + 1; i < RD; i++) {
+      const double f = a[i][cc] / a[cc][cc];
+#pragma unroll
+      for (int j = cc; j < 2 * RD; j++) a[i][j] -= f * a[cc][j];
+    }
+  }
+#pragma unroll
+  for (int cc = RD - 1; cc >= 0; cc--)
+#pragma unroll
+    for (int j = 0; j < RD; j++) {
+      double s = a[cc][RD + j];
+#pragma unroll
+      for (int k = cc + 1; k < RD; k++) s -= a[cc][k] * a[k][RD + j];
+      a[cc][RD + j] = s / a[cc][cc];
+    }
+  double mahal = 0;
+#pragma unroll
+  for (int j = 0; j < RD; j++) {
+    double s = 0;
+#pragma unroll
+    for (int i = 0; i < RD; i++) {
+      Si[i][j] = a[i][RD + j];
+      s += res[i] * a[i][RD + j];
+    }
+    mahal += s * res[j];
+  }
+  return mahal;
+}
+
+template <int G, int RD>
+__device__ int update_core(Ctx<G>& c, const KParams& p, const viekf_event& E, int n, int len) {
+  const double* Hc = c.sm + SM_HC;
+  const double* res = c.sm + SM_RES;
+  int* cols = c.sc + SC_COUNT;
+  const int m = cols[6];
+  UpdVec<G> v(c, 16 + 3 * p.N);
+  // ---- P H^T: gather of <= 6 columns of P ----
+  for (int i = c.tid; i < n; i += G) {
+    double s[3] = {0, 0, 0};
+    for (int k = 0; k < m; k++) {
+      const double pv = c.P[psym(i, cols[k])];
+#pragma unroll
+      for (int a = 0; a < RD; a++) s[a] = fma(pv, Hc[a * 6 + k], s[a]);
+    }
+    v.Hv[i] = make_double2(s[0], s[1]);
+    if (RD == 3) v.H2[i] = s[2];
+  }
+  c.sync();
+  // ---- S = H P H^T + R, S^-1, Mahalanobis gate: every thread evaluates the same registers, no broadcast needed ----
+  double S[3][3], Si[3][3];
+#pragma unroll
+  for (int a = 0; a < RD; a++)
+#pragma unroll
+    for (int b = 0; b < RD; b++) {
+      double s = 0;
+      for (int k = 0; k < m; k++) {
+        const int ck = cols[k];
+        const double ph = (b == 0) ? v.Hv[ck].x : (b == 1 ? v.Hv[ck].y : v.H2[ck]);
+        s += Hc[a * 6 + k] * ph;
+      }
+      S[a][b] = s + E.R[a + b * RD];
+    }
+  const double mahal = inverse_and_mahal<RD>(S, Si, res);
+  if (mahal > 9.0) {
+    if (c.tid == 0) c.sc[SC_NGATED] += 1;
+    return VIEKF_MEAS_GATED;  // early return: no fix_depth (vi_ekf_meas.cpp:238)
+  }
+  // ---- K = P H^T S^-1, K S, state correction lambda o (K r) ----
+  bool bad = false;
+  for (int i = c.tid; i < n; i += G) {
+    const double2 h01 = v.Hv[i];
+    double ph[3] = {h01.x, h01.y, 0.0};
+    if (RD == 3) ph[2] = v.H2[i];
+    double k3[3] = {0, 0, 0}, ks[3] = {0, 0, 0};
+#pragma unroll
+    for (int b = 0; b < RD; b++) {
+      double s = 0;
+#pragma unroll
+      for (int a = 0; a < RD; a++) s += ph[a] * Si[a][b];
+      k3[b] = s;
+      bad |= (s != s);
+    }
+    double d = 0;
+#pragma unroll
+    for (int a = 0; a < RD; a++) d += k3[a] * res[a];
+#pragma unroll
+    for (int a = 0; a < RD; a++) {
+      double s = 0;
+#pragma unroll
+      for (int b = 0; b < RD; b++) s += k3[b] * S[b][a];
+      ks[a] = s;
+    }
+    v.Kv[i] = make_double2(k3[0], k3[1]);
+    v.KSv[i] = make_double2(ks[0], ks[1]);
+    if (RD == 3) {
+      v.K2[i] = k3[2];
+      v.KS2[i] = ks[2];
+    }
+    const double li = c.lam[i];
+    v.av[i] = p.use_partial ? 1.0 - li : 0.0;
+    c.dx[i] = p.use_partial ? li * d : d;
+  }
+  if (bad) atomicOr((unsigned*)&cols[8], 1u);
+  c.sync();
+  if (!cols[8]) {
+    boxplus_inplace(c, c.dx, 1.0, len);
+    rank_update<G, RD>(c, v, n);
+  } else if (c.tid == 0) {
+    c.sc[SC_FLAGS] |= VIEKF_FLAG_NAN_GAIN;
+    c.sc[SC_NNAN] += 1;
+  }
+  c.sync();
+  for (int i = c.tid; i < len; i += G) fix_depth_one(c, p, i);
+  return VIEKF_MEAS_SUCCESS;
+}
+
 // update(meas) with add_measurement's bookkeeping in front (vi_ekf_meas.cpp:130-147,196-278). Returns meas_result_t.
 template <int G>
 __device__ int ev_update(Ctx<G>& c, const KParams& p, const viekf_event& E) {
-  const double* zv = c.sm + SM_ZV;
+  const double* zv = (E.aux == 1) ? (c.sm + SM_UB) : c.zv;
   const int type = E.type, zdim = E.zdim, rd = E.rdim;
   for (int k = 0; k < zdim; k++)
     if (zv[k] != zv[k]) return VIEKF_MEAS_NAN;
@@ -788,11 +983,8 @@ __device__ int ev_update(Ctx<G>& c, const KParams& p, const viekf_event& E) {
   const int len = c.sc[SC_LEN];
   const int n = 16 + 3 * len;
   double* Hc = c.sm + SM_HC;   // [3][6]
-  double* S = c.sm + SM_S;     // [3][3] row-major
-  double* Si = c.sm + SM_SI;   // [3][3]
   double* res = c.sm + SM_RES; // [4]
   int* cols = c.sc + SC_COUNT; // [6] + m + gate + nan
-  c.sync();
   // ---- h, H (sparse columns), residual: thread 0 ----
   if (c.tid == 0) {
     const double* x = c.x;
@@ -896,109 +1088,13 @@ __device__ int ev_update(Ctx<G>& c, const KParams& p, const viekf_event& E) {
     if (hn) cols[8] = 1;
   }
   c.sync();
-  if (E.active) {
-    const int m = cols[6];
-    double* PHt = c.upd;
-    double* K = c.upd + 3 * n;
-    double* KS = c.upd + 6 * n;
-    // ---- P H^T: gather of <= 6 columns of P ----
-    for (int i = c.tid; i < n; i += G) {
-      double s[3] = {0, 0, 0};
-      for (int k = 0; k < m; k++) {
-        const double pv = c.P[psym(i, cols[k])];
-        for (int a = 0; a < 3; a++) s[a] += pv * Hc[a * 6 + k];
-      }
-      for (int a = 0; a < 3; a++) PHt[i * 3 + a] = s[a];
-    }
-    c.sync();
-    // ---- S = H P H^T + R, S^-1 by partial-pivot LU (what Eigen's dynamic inverse does), Mahalanobis gate ----
-    if (c.tid == 0) {
-      double a[3][6];
-      for (int i = 0; i < rd; i++)
-        for (int j = 0; j < rd; j++) {
-          double s = 0;
-          for (int k = 0; k < m; k++) s += Hc[i * 6 + k] * PHt[cols[k] * 3 + j];
-          s += E.R[i + j * rd];
-          S[i * 3 + j] = s;
-          a[i][j] = s;
-          a[i][j + rd] = (i == j) ? 1.0 : 0.0;
-        }
-      for (int cc = 0; cc < rd; cc++) {
-        int pv = cc;
-        for (int i = cc + 1; i < rd; i++)
-          if (fabs(a[i][cc]) > fabs(a[pv][cc])) pv = i;
-        if (pv != cc)
-          for (int j = 0; j < 2 * rd; j++) {
-            const double t = a[cc][j];
-            a[cc][j] = a[pv][j];
-            a[pv][j] = t;
-          }
-        for (int i = cc + 1; i < rd; i++) {
-          const double f = a[i][cc] / a[cc][cc];
-          for (int j = cc; j < 2 * rd; j++) a[i][j] -= f * a[cc][j];
-        }
-      }
-      for (int cc = rd - 1; cc >= 0; cc--)
-        for (int j = 0; j < rd; j++) {
-          double s = a[cc][rd + j];
-          for (int k = cc + 1; k < rd; k++) s -= a[cc][k] * a[k][rd + j];
-          a[cc][rd + j] = s / a[cc][cc];
-        }
-      double mahal = 0;
-      for (int j = 0; j < rd; j++) {
-        double s = 0;
-        for (int i = 0; i < rd; i++) {
-          Si[i * 3 + j] = a[i][rd + j];
-          s += res[i] * a[i][rd + j];
-        }
-        mahal += s * res[j];
-      }
-      if (mahal > 9.0) {
-        cols[7] = 1;
-        c.sc[SC_NGATED] += 1;
-      }
-    }
-    c.sync();
-    if (cols[7]) return VIEKF_MEAS_GATED;  // early return: no fix_depth (vi_ekf_meas.cpp:238)
-    // ---- K = P H^T S^-1, K S, state correction lambda o (K r) ----
-    bool bad = false;
-    for (int i = c.tid; i < n; i += G) {
-      double k3[3] = {0, 0, 0};
-      for (int bb = 0; bb < rd; bb++) {
-        double s = 0;
-        for (int a = 0; a < rd; a++) s += PHt[i * 3 + a] * Si[a * 3 + bb];
-        k3[bb] = s;
-        bad |= (s != s);
-      }
-      double d = 0;
-      for (int a = 0; a < rd; a++) d += k3[a] * res[a];
-      for (int a = 0; a < 3; a++) {
-        double s = 0;
-        for (int bb = 0; bb < rd; bb++) s += k3[bb] * S[bb * 3 + a];
-        K[i * 3 + a] = k3[a];
-        KS[i * 3 + a] = (a < rd) ? s : 0.0;
-      }
-      c.dx[i] = p.use_partial ? c.lam[i] * d : d;
-    }
-    if (bad) atomicOr((unsigned*)&cols[8], 1u);
-    c.sync();
-    if (!cols[8]) {
-      boxplus_inplace(c, c.dx, 1.0, len);
-      if (rd == 1)
-        rank_update<G, 1>(c, n, p.use_partial != 0);
-      else if (rd == 2)
-        rank_update<G, 2>(c, n, p.use_partial != 0);
-      else
-        rank_update<G, 3>(c, n, p.use_partial != 0);
-    } else if (c.tid == 0) {
-      c.sc[SC_FLAGS] |= VIEKF_FLAG_NAN_GAIN;
-      c.sc[SC_NNAN] += 1;
-    }
-    c.sync();
+  if (!E.active) {  // logged only: no gate, no correction, but fix_depth still runs (vi_ekf_meas.cpp:230,271)
+    for (int i = c.tid; i < len; i += G) fix_depth_one(c, p, i);
+    return VIEKF_MEAS_SUCCESS;
   }
-  for (int i = c.tid; i < len; i += G) fix_depth_one(c, p, i);
-  c.sync();
-  return VIEKF_MEAS_SUCCESS;
+  if (rd == 1) return update_core<G, 1>(c, p, E, n, len);
+  if (rd == 2) return update_core<G, 2>(c, p, E, n, len);
+  return update_core<G, 3>(c, p, E, n, len);
 }
 
 // ------------------------------------------------------------------------------------------------------------------
@@ -1078,11 +1174,33 @@ __device__ void ev_stat(Ctx<G>& c, const KParams& p, const viekf_event& E, int64
   c.sync();
 }
 
+// Resolves component k of event e for this instance: shared z | per-instance value block, plus generated white noise and
+// (PROP) the instance's constant IMU bias (include/viekf_batch.h: viekf_event.sigma, viekf_tape.seed / imu_bias_range).
+__device__ __forceinline__ void resolve_values(const KParams& p, int64_t e, int64_t b, int64_t ginst, int k, double* out) {
+  const viekf_event& E = p.ev[e];
+  const int kind = E.kind;
+  if (!(kind == VIEKF_EV_PROP || kind == VIEKF_EV_UPD || kind == VIEKF_EV_INIT)) return;
+  double v = (E.noise >= 0 && p.values) ? p.values[b * p.vstride + 8 * (int64_t)E.noise + k] : E.z[k];
+  if (p.seed) {
+    const double sg = E.sigma[k];
+    const double sgo = E.sigma[k ^ 1];
+    if (sg != 0.0 || sgo != 0.0) {
+      double nn[2];
+      const uint32_t key = (kind == VIEKF_EV_PROP && E.aux >= 0) ? (0x80000000u | (uint32_t)E.aux) : (uint32_t)e;
+      viekf_normal_pair(p.seed, (uint64_t)ginst, key, (uint32_t)(k >> 1), nn);
+      v += sg * nn[k & 1];
+    }
+    if (kind == VIEKF_EV_PROP && k < 6 && p.bias_range[k] != 0.0)
+      v += p.bias_range[k] * viekf_uniform_pm1(p.seed, (uint64_t)ginst, VIEKF_NOISE_EVENT_BIAS, k);
+  }
+  out[k] = v;
+}
+
 // ------------------------------------------------------------------------------------------------------------------
 // the persistent tape executor
 // ------------------------------------------------------------------------------------------------------------------
 template <int G>
-__global__ void __launch_bounds__((G >= 128 ? G : 128)) viekf_tape_kernel(const __grid_constant__ KParams p) {
+__global__ void __launch_bounds__((G >= 128 ? G : 128), (G == 128 ? 3 : (G == 256 ? 2 : 1))) viekf_tape_kernel(const __grid_constant__ KParams p) {
   extern __shared__ __align__(16) double smem[];
   constexpr int CTA = (G >= 128 ? G : 128);
   constexpr int GPC = CTA / G;
@@ -1091,7 +1209,7 @@ __global__ void __launch_bounds__((G >= 128 ? G : 128)) viekf_tape_kernel(const 
   c.gi = threadIdx.x / G;
   c.tid = threadIdx.x % G;
   double* base = smem + (size_t)c.gi * L.total;
-  c.x = base + L.x; c.P = base + L.P; c.lam = base + L.lam; c.dx = base + L.dx; c.Abd = base + L.Abd; c.T = base + L.T;
+  c.x = base + L.x; c.P = base + L.P; c.lam = base + L.lam; c.dx = base + L.dx; c.Abd = base + L.Abd; c.AbT = base + L.AbT; c.T = base + L.T;
   c.Ac = base + L.Ac; c.Gb = base + L.Gb; c.Afd = base + L.Afd; c.Gd = base + L.Gd; c.Y = base + L.Y; c.upd = base + L.upd;
   c.sm = base + L.small;
   c.ids = (int*)(base + L.ids);
@@ -1125,33 +1243,17 @@ __global__ void __launch_bounds__((G >= 128 ? G : 128)) viekf_tape_kernel(const 
       const int np2 = (n0 * (n0 + 1) / 2 + 1) >> 1;
       for (int i = c.tid; i < np2; i += G) sP[i] = gP[i];
     }
+    if (p.ev_count > 0 && c.tid < 8) resolve_values(p, p.ev_first, b, ginst, c.tid, c.sm + SM_ZV);
     c.sync();
     // ---- run the tape slice ----
     for (int64_t e = p.ev_first; e < p.ev_first + p.ev_count; e++) {
       const viekf_event& E = p.ev[e];
       const int kind = E.kind;
-      // resolve this instance's values for the event: shared z | per-instance block, plus generated noise
-      if (kind == VIEKF_EV_PROP || kind == VIEKF_EV_UPD || kind == VIEKF_EV_INIT) {
-        if (c.tid < 8) {
-          const int k = c.tid;
-          double v = (E.noise >= 0 && p.values) ? p.values[b * p.vstride + 8 * (int64_t)E.noise + k] : E.z[k];
-          if (p.seed) {
-            const double sg = E.sigma[k];
-            const double sgo = E.sigma[k ^ 1];
-            if (sg != 0.0 || sgo != 0.0) {
-              double nn[2];
-              const uint32_t key = (kind == VIEKF_EV_PROP && E.aux >= 0) ? (0x80000000u | (uint32_t)E.aux) : (uint32_t)e;
-              viekf_normal_pair(p.seed, (uint64_t)ginst, key, (uint32_t)(k >> 1), nn);
-              v += sg * nn[k & 1];
-            }
-            if (kind == VIEKF_EV_PROP && k < 6 && p.bias_range[k] != 0.0)
-              v += p.bias_range[k] * viekf_uniform_pm1(p.seed, (uint64_t)ginst, VIEKF_NOISE_EVENT_BIAS, k);
-          }
-          if (kind == VIEKF_EV_UPD && E.aux == 1 && k < 6) v = c.sm[SM_UB + k];
-          c.sm[SM_ZV + k] = v;
-        }
-        c.sync();
-      }
+      // this event's values were resolved while the previous event ran; resolve the next event's now (8 lanes of the
+      // last warp), into the other buffer: the barrier that ends this event publishes them
+      c.zv = c.sm + SM_ZV + 8 * (int)((e - p.ev_first) & 1);
+      if (e + 1 < p.ev_first + p.ev_count && c.tid >= G - 32 && (c.tid & 31) < 8)
+        resolve_values(p, e + 1, b, ginst, c.tid & 31, c.sm + SM_ZV + 8 * (int)((e + 1 - p.ev_first) & 1));
       int result = VIEKF_MEAS_NONE;
       switch (kind) {
         case VIEKF_EV_PROP:
@@ -1161,7 +1263,7 @@ __global__ void __launch_bounds__((G >= 128 ? G : 128)) viekf_tape_kernel(const 
           result = ev_update(c, p, E);
           break;
         case VIEKF_EV_INIT:
-          result = do_init_feature(c, p, c.sm[SM_ZV], c.sm[SM_ZV + 1], E.z[4]) ? 1 : 0;
+          result = do_init_feature(c, p, c.zv[0], c.zv[1], E.z[4]) ? 1 : 0;
           break;
         case VIEKF_EV_CLEAR:
           do_clear_feature(c, p, find_feature(c, E.id));
@@ -1211,6 +1313,8 @@ static cudaError_t launch_g(const KParams& p, int sm_count, cudaStream_t stream)
   constexpr int GPC = CTA / G;
   const size_t smem = smem_bytes_per_filter(p.N) * GPC;
   cudaError_t e = cudaFuncSetAttribute(viekf_tape_kernel<G>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  if (e != cudaSuccess) return e;
+  e = cudaFuncSetAttribute(viekf_tape_kernel<G>, cudaFuncAttributePreferredSharedMemoryCarveout, (int)cudaSharedmemCarveoutMaxShared);
   if (e != cudaSuccess) return e;
   int occ = 0;
   e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, viekf_tape_kernel<G>, CTA, smem);
