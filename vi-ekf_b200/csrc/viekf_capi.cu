@@ -153,7 +153,7 @@ int viekf_batch_create(const viekf_config* cfg, int64_t B, int32_t N, int32_t de
   h->group = vk::group_size_for(N);
   if (const char* g = getenv("VIEKF_GROUP")) {
     const int v = atoi(g);
-    if (v == 32 || v == 64 || v == 128 || v == 256) h->group = v;
+    if (v == 32 || v == 64 || v == 128 || v == 192 || v == 256) h->group = v;
   }
   const size_t need = vk::smem_bytes_per_filter(N) * ((h->group >= 128 ? h->group : 128) / h->group);
   if (need > (size_t)prop.sharedMemPerBlockOptin) {

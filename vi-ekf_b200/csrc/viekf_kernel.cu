@@ -499,9 +499,14 @@ __device__ void ev_propagate(Ctx<G>& c, const KParams& p, const viekf_event& E) 
 // ------------------------------------------------------------------------------------------------------------------
 template <int G>
 __device__ int find_feature(const Ctx<G>& c, int id) {
+  // global_to_local_feature_id (vi_ekf_helper.cpp:114-125): every warp searches the id list with one ballot per 32 ids
   const int len = c.sc[SC_LEN];
-  for (int i = 0; i < len; i++)
-    if (c.ids[i] == id) return i;
+  const int lane = c.tid & 31;
+  for (int base = 0; base < len; base += 32) {
+    const int i = base + lane;
+    const unsigned hit = __ballot_sync(0xffffffffu, i < len && c.ids[i] == id);
+    if (hit) return base + __ffs(hit) - 1;
+  }
   return -1;
 }
 
@@ -685,28 +690,33 @@ __device__ void do_keyframe_reset(Ctx<G>& c, const KParams& p) {
 template <int G>
 __device__ void do_keep_only(Ctx<G>& c, const KParams& p, const int32_t* feats, int nf) {
   c.sync();
-  if (c.tid == 0) {
+  // one thread per tracked feature decides keep / drop and keyframe overlap; thread 0 then lists the drops in order
+  int* keepf = (int*)c.upd;  // [N] flags, update workspace is idle here
+  if (c.tid == 0) c.sc[SC_TMP1] = 0;
+  c.sync();
+  {
     const int len = c.sc[SC_LEN];
     const int nkf = c.sc[SC_NKF];
     const int32_t* kf = p.kf_ids + c.b * KF_CAP;
-    int nrm = 0, overlap = 0;
-    for (int l = 0; l < len; l++) {
+    for (int l = c.tid; l < len; l += G) {
+      const int id = c.ids[l];
       bool keep = false;
-      for (int i = 0; i < nf; i++)
-        if (c.ids[l] == feats[i]) {
-          keep = true;
-          if (p.use_kfreset)
-            for (int j = 0; j < nkf; j++)
-              if (kf[j] == feats[i]) {
-                overlap++;
-                break;
-              }
-          break;
-        }
-      if (!keep) c.rm[nrm++] = c.ids[l];
+      for (int i = 0; i < nf; i++) keep |= (feats[i] == id);
+      if (keep && p.use_kfreset) {
+        bool ov = false;
+        for (int j = 0; j < nkf; j++) ov |= (kf[j] == id);
+        if (ov) atomicAdd(&c.sc[SC_TMP1], 1);
+      }
+      keepf[l] = keep ? 1 : 0;
     }
+  }
+  c.sync();
+  if (c.tid == 0) {
+    const int len = c.sc[SC_LEN];
+    int nrm = 0;
+    for (int l = 0; l < len; l++)
+      if (!keepf[l]) c.rm[nrm++] = c.ids[l];
     c.sc[SC_TMP0] = nrm;
-    c.sc[SC_TMP1] = overlap;
   }
   c.sync();
   const int nrm = c.sc[SC_TMP0];
@@ -750,7 +760,7 @@ struct UpdVec {
 };
 
 template <int G, int RD>
-__device__ __forceinline__ void rank_update(const Ctx<G>& c, const UpdVec<G>& v, int n) {
+__device__ __noinline__ void rank_update(const Ctx<G>& c, const UpdVec<G>& v, int n) {
   const int lane = c.tid & 31, warp = c.tid >> 5;
   constexpr int NW = G / 32;
   constexpr int RB = 4;
@@ -874,40 +884,59 @@ __device__ __forceinline__ double inverse_and_mahal(const double (&S)[3][3], dou
   return mahal;
 }
 
-template <int G, int RD>
-__device__ int update_core(Ctx<G>& c, const KParams& p, const viekf_event& E, int n, int len) {
-  const double* Hc = c.sm + SM_HC;
-  const double* res = c.sm + SM_RES;
+// The measurement Jacobian in registers: RD rows on MC (static) candidate columns, m of them live.
+template <int RD, int MC>
+struct HReg {
+  double h[RD * MC];
+  int col[MC];
+  int m;
+  double res[RD];
+  bool hnan;
+};
+
+template <int G, int RD, int MC>
+__device__ int update_core(Ctx<G>& c, const KParams& p, const viekf_event& E, int n, int len, const HReg<RD, MC>& H) {
   int* cols = c.sc + SC_COUNT;
-  const int m = cols[6];
   UpdVec<G> v(c, 16 + 3 * p.N);
-  // ---- P H^T: gather of <= 6 columns of P ----
+  // ---- P H^T: gather of <= MC columns of P ----
   for (int i = c.tid; i < n; i += G) {
     double s[3] = {0, 0, 0};
-    for (int k = 0; k < m; k++) {
-      const double pv = c.P[psym(i, cols[k])];
 #pragma unroll
-      for (int a = 0; a < RD; a++) s[a] = fma(pv, Hc[a * 6 + k], s[a]);
-    }
+    for (int k = 0; k < MC; k++)
+      if (k < H.m) {
+        const double pv = c.P[psym(i, H.col[k])];
+#pragma unroll
+        for (int a = 0; a < RD; a++) s[a] = fma(pv, H.h[a * MC + k], s[a]);
+      }
     v.Hv[i] = make_double2(s[0], s[1]);
     if (RD == 3) v.H2[i] = s[2];
   }
+  if (c.tid == 0) cols[8] = H.hnan ? 1 : 0;
   c.sync();
   // ---- S = H P H^T + R, S^-1, Mahalanobis gate: every thread evaluates the same registers, no broadcast needed ----
   double S[3][3], Si[3][3];
+  {
+    double ph[MC][3];
 #pragma unroll
-  for (int a = 0; a < RD; a++)
-#pragma unroll
-    for (int b = 0; b < RD; b++) {
-      double s = 0;
-      for (int k = 0; k < m; k++) {
-        const int ck = cols[k];
-        const double ph = (b == 0) ? v.Hv[ck].x : (b == 1 ? v.Hv[ck].y : v.H2[ck]);
-        s += Hc[a * 6 + k] * ph;
-      }
-      S[a][b] = s + E.R[a + b * RD];
+    for (int k = 0; k < MC; k++) {
+      const int ck = (k < H.m) ? H.col[k] : 0;
+      const double2 t = v.Hv[ck];
+      ph[k][0] = t.x;
+      ph[k][1] = t.y;
+      ph[k][2] = (RD == 3) ? v.H2[ck] : 0.0;
     }
-  const double mahal = inverse_and_mahal<RD>(S, Si, res);
+#pragma unroll
+    for (int a = 0; a < RD; a++)
+#pragma unroll
+      for (int b = 0; b < RD; b++) {
+        double s = 0;
+#pragma unroll
+        for (int k = 0; k < MC; k++)
+          if (k < H.m) s += H.h[a * MC + k] * ph[k][b];
+        S[a][b] = s + E.R[a + b * RD];
+      }
+  }
+  const double mahal = inverse_and_mahal<RD>(S, Si, H.res);
   if (mahal > 9.0) {
     if (c.tid == 0) c.sc[SC_NGATED] += 1;
     return VIEKF_MEAS_GATED;  // early return: no fix_depth (vi_ekf_meas.cpp:238)
@@ -929,7 +958,7 @@ __device__ int update_core(Ctx<G>& c, const KParams& p, const viekf_event& E, in
     }
     double d = 0;
 #pragma unroll
-    for (int a = 0; a < RD; a++) d += k3[a] * res[a];
+    for (int a = 0; a < RD; a++) d += k3[a] * H.res[a];
 #pragma unroll
     for (int a = 0; a < RD; a++) {
       double s = 0;
@@ -961,6 +990,27 @@ __device__ int update_core(Ctx<G>& c, const KParams& p, const viekf_event& E, in
   return VIEKF_MEAS_SUCCESS;
 }
 
+// generic path: H, columns and residual were written to shared memory by thread 0
+template <int G, int RD>
+__device__ int update_generic(Ctx<G>& c, const KParams& p, const viekf_event& E, int n, int len) {
+  const double* Hc = c.sm + SM_HC;
+  const double* res = c.sm + SM_RES;
+  const int* cols = c.sc + SC_COUNT;
+  HReg<RD, 6> H;
+  H.m = cols[6];
+  H.hnan = cols[8] != 0;
+#pragma unroll
+  for (int k = 0; k < 6; k++) {
+    H.col[k] = cols[k];
+#pragma unroll
+    for (int a = 0; a < RD; a++) H.h[a * 6 + k] = Hc[a * 6 + k];
+  }
+#pragma unroll
+  for (int a = 0; a < RD; a++) H.res[a] = res[a];
+  c.sync();  // cols[8] is re-armed inside update_core
+  return update_core<G, RD, 6>(c, p, E, n, len, H);
+}
+
 // update(meas) with add_measurement's bookkeeping in front (vi_ekf_meas.cpp:130-147,196-278). Returns meas_result_t.
 template <int G>
 __device__ int ev_update(Ctx<G>& c, const KParams& p, const viekf_event& E) {
@@ -982,10 +1032,68 @@ __device__ int ev_update(Ctx<G>& c, const KParams& p, const viekf_event& E) {
   }
   const int len = c.sc[SC_LEN];
   const int n = 16 + 3 * len;
+  if (!E.active) {  // logged only: no gate, no correction, but fix_depth still runs (vi_ekf_meas.cpp:230,271)
+    c.sync();
+    for (int i = c.tid; i < len; i += G) fix_depth_one(c, p, i);
+    return VIEKF_MEAS_SUCCESS;
+  }
+  // ---- the three models the Monte-Carlo path lives on keep h, H and the residual in registers: every thread evaluates
+  //      them from the same shared state, so no thread-0 section and no broadcast barrier ----
+  if (type == VIEKF_FEAT && rd == 2) {  // h_feat, vi_ekf_meas.cpp:354-367
+    const double* x = c.x;
+    HReg<2, 2> H;
+    H.m = 2;
+    H.col[0] = 16 + 3 * fi;
+    H.col[1] = H.col[0] + 1;
+    V3 ze, T0, T1;
+    zeta_T(ldq(x + 17 + 5 * fi), ze, T0, T1);
+    const double ez = ze.z;
+    H.res[0] = zv[0] - (p.fl[0] * ze.x / ez + p.cc[0]);
+    H.res[1] = zv[1] - (p.fl[1] * ze.y / ez + p.cc[1]);
+    const double zz[3] = {ze.x, ze.y, ze.z};
+    const double sk[9] = {0, -ze.z, ze.y, ze.z, 0, -ze.x, -ze.y, ze.x, 0};
+    const double Tm[6] = {T0.x, T1.x, T0.y, T1.y, T0.z, T1.z};
+#pragma unroll
+    for (int a = 0; a < 2; a++) {
+      double fb[3], fbs[3];
+#pragma unroll
+      for (int k = 0; k < 3; k++) fb[k] = (1.0 / ez) * p.fl[a] * (((k == 2) ? zz[a] : 0.0) / ez - (a == k ? 1.0 : 0.0));
+#pragma unroll
+      for (int k = 0; k < 3; k++) fbs[k] = fb[0] * sk[k] + fb[1] * sk[3 + k] + fb[2] * sk[6 + k];
+#pragma unroll
+      for (int bb = 0; bb < 2; bb++) H.h[a * 2 + bb] = fbs[0] * Tm[bb] + fbs[1] * Tm[2 + bb] + fbs[2] * Tm[4 + bb];
+    }
+    H.hnan = (H.h[0] != H.h[0]) || (H.h[1] != H.h[1]) || (H.h[2] != H.h[2]) || (H.h[3] != H.h[3]);
+    return update_core<G, 2, 2>(c, p, E, n, len, H);
+  }
+  if (type == VIEKF_ACC && p.use_drag && rd == 2) {  // h_acc drag model, vi_ekf_meas.cpp:281-296
+    const double* x = c.x;
+    const double mu = x[16];
+    HReg<2, 5> H;
+    H.m = 5;
+    H.col[0] = 3; H.col[1] = 4; H.col[2] = 9; H.col[3] = 10; H.col[4] = 15;
+#pragma unroll
+    for (int k = 0; k < 10; k++) H.h[k] = 0.0;
+    H.h[0] = -mu; H.h[2] = 1.0; H.h[4] = -x[3];
+    H.h[5 + 1] = -mu; H.h[5 + 3] = 1.0; H.h[5 + 4] = -x[4];
+    H.res[0] = zv[0] - (-mu * x[3] + x[10]);
+    H.res[1] = zv[1] - (-mu * x[4] + x[11]);
+    H.hnan = (mu != mu) || (x[3] != x[3]) || (x[4] != x[4]);
+    return update_core<G, 2, 5>(c, p, E, n, len, H);
+  }
+  if (type == VIEKF_ALT && rd == 1) {  // h_alt, vi_ekf_meas.cpp:308-315
+    HReg<1, 1> H;
+    H.m = 1;
+    H.col[0] = 2;
+    H.h[0] = -1.0;
+    H.res[0] = zv[0] - (-c.x[2]);
+    H.hnan = false;
+    return update_core<G, 1, 1>(c, p, E, n, len, H);
+  }
   double* Hc = c.sm + SM_HC;   // [3][6]
   double* res = c.sm + SM_RES; // [4]
   int* cols = c.sc + SC_COUNT; // [6] + m + gate + nan
-  // ---- h, H (sparse columns), residual: thread 0 ----
+  // ---- every other model: h, H (sparse columns), residual by thread 0 into shared memory ----
   if (c.tid == 0) {
     const double* x = c.x;
     for (int k = 0; k < 18; k++) Hc[k] = 0.0;
@@ -1088,18 +1196,45 @@ __device__ int ev_update(Ctx<G>& c, const KParams& p, const viekf_event& E) {
     if (hn) cols[8] = 1;
   }
   c.sync();
-  if (!E.active) {  // logged only: no gate, no correction, but fix_depth still runs (vi_ekf_meas.cpp:230,271)
-    for (int i = c.tid; i < len; i += G) fix_depth_one(c, p, i);
-    return VIEKF_MEAS_SUCCESS;
-  }
-  if (rd == 1) return update_core<G, 1>(c, p, E, n, len);
-  if (rd == 2) return update_core<G, 2>(c, p, E, n, len);
-  return update_core<G, 3>(c, p, E, n, len);
+  if (rd == 1) return update_generic<G, 1>(c, p, E, n, len);
+  if (rd == 2) return update_generic<G, 2>(c, p, E, n, len);
+  return update_generic<G, 3>(c, p, E, n, len);
 }
 
 // ------------------------------------------------------------------------------------------------------------------
 // STAT
 // ------------------------------------------------------------------------------------------------------------------
+// e^T B^-1 e for the M x M block B of P picked by idx (M = 16: base error state, M = 6: position + attitude), by a
+// right-looking Cholesky spread over the lanes of one warp: lane i owns row i.  The subtractions hit every element in
+// the same k-ascending order as a scalar left-looking factorisation.  NaN when B is not positive definite.
+template <int M>
+__device__ __forceinline__ double nees_warp(const double* P, const double* er, int lane) {
+  auto idx = [](int i) { return (M == 16) ? i : (i < 3 ? i : i + 3); };
+  const int li = lane < M ? lane : M - 1;
+  double a[M];
+#pragma unroll
+  for (int j = 0; j < M; j++) a[j] = (lane < M && j <= lane) ? P[psym(idx(li), idx(j))] : 0.0;
+  double r = (lane < M) ? er[idx(li)] : 0.0;
+  double q = 0;
+  bool bad = false;
+#pragma unroll
+  for (int j = 0; j < M; j++) {
+    const double sjj = __shfl_sync(0xffffffffu, a[j], j);
+    bad |= !(sjj > 0.0);
+    const double ljj = sqrt(sjj);
+    const double lij = (lane == j) ? ljj : a[j] / ljj;
+    const double yj = __shfl_sync(0xffffffffu, r / ljj, j);
+    q += yj * yj;
+    if (lane > j) r -= lij * yj;
+#pragma unroll
+    for (int k = j + 1; k < M; k++) {
+      const double lkj = __shfl_sync(0xffffffffu, lij, k);
+      if (lane >= k) a[k] -= lij * lkj;
+    }
+  }
+  return bad ? nan("") : q;
+}
+
 template <int G>
 __device__ void ev_stat(Ctx<G>& c, const KParams& p, const viekf_event& E, int64_t ginst) {
   if (!p.stats || E.id < 0 || E.id >= p.n_buckets) return;
@@ -1129,34 +1264,14 @@ __device__ void ev_stat(Ctx<G>& c, const KParams& p, const viekf_event& E, int64
     for (int i = 0; i < 7; i++) er[9 + i] = xt[10 + i] - x[10 + i];
   }
   c.sync();
-  // NEES by Cholesky of the 16x16 base block (thread 0) and of the 6x6 pose block (thread 1 or 0)
-  if (c.tid < 2 && (G > 1)) {
-    const int m = (c.tid == 0) ? 16 : 6;
-    const int pose[6] = {0, 1, 2, 6, 7, 8};
-    double L[136];
-    double y[16];
-    double qv = 0;
-    bool bad = false;
-    for (int i = 0; i < m; i++) {
-      const int ii = (c.tid == 0) ? i : pose[i];
-      for (int j = 0; j <= i; j++) {
-        const int jj = (c.tid == 0) ? j : pose[j];
-        double s = c.P[psym(ii, jj)];
-        for (int k = 0; k < j; k++) s -= L[plo(i, k)] * L[plo(j, k)];
-        if (i == j) {
-          if (!(s > 0.0)) bad = true;  // not positive definite (e.g. right after a keyframe reset): NEES undefined
-          L[plo(i, j)] = sqrt(s);
-        } else {
-          L[plo(i, j)] = s / L[plo(j, j)];
-        }
-      }
-      if (bad) break;
-      double s = er[ii];
-      for (int k = 0; k < i; k++) s -= L[plo(i, k)] * y[k];
-      y[i] = s / L[plo(i, i)];
-      qv += y[i] * y[i];
-    }
-    out[c.tid] = bad ? nan("") : qv;
+  // NEES by Cholesky of the 16x16 base block (warp 0) and of the 6x6 pose block (warp 1, or warp 0 again)
+  if (c.tid < 32) {
+    const double q16 = nees_warp<16>(c.P, er, c.tid);
+    if (c.tid == 0) out[0] = q16;
+  }
+  if (G >= 64 ? (c.tid >= 32 && c.tid < 64) : (c.tid < 32)) {
+    const double q6 = nees_warp<6>(c.P, er, c.tid & 31);
+    if ((c.tid & 31) == 0) out[1] = q6;
   }
   c.sync();
   double* st = p.stats + (size_t)E.id * VIEKF_STAT_WIDTH;
@@ -1200,7 +1315,7 @@ __device__ __forceinline__ void resolve_values(const KParams& p, int64_t e, int6
 // the persistent tape executor
 // ------------------------------------------------------------------------------------------------------------------
 template <int G>
-__global__ void __launch_bounds__((G >= 128 ? G : 128), (G == 128 ? 3 : (G == 256 ? 2 : 1))) viekf_tape_kernel(const __grid_constant__ KParams p) {
+__global__ void __launch_bounds__((G >= 128 ? G : 128), (G == 128 ? 3 : (G == 192 ? 3 : (G == 256 ? 3 : 1)))) viekf_tape_kernel(const __grid_constant__ KParams p) {
   extern __shared__ __align__(16) double smem[];
   constexpr int CTA = (G >= 128 ? G : 128);
   constexpr int GPC = CTA / G;
@@ -1333,6 +1448,7 @@ cudaError_t launch_tape(const KParams& p, int group, int sm_count, cudaStream_t 
     case 32: return launch_g<32>(p, sm_count, stream);
     case 64: return launch_g<64>(p, sm_count, stream);
     case 128: return launch_g<128>(p, sm_count, stream);
+    case 192: return launch_g<192>(p, sm_count, stream);
     case 256: return launch_g<256>(p, sm_count, stream);
     default: return cudaErrorInvalidValue;
   }
