@@ -154,8 +154,10 @@ int viekf_batch_create(const viekf_config* cfg, int64_t B, int32_t N, int32_t de
   if (const char* g = getenv("VIEKF_GROUP")) {
     const int v = atoi(g);
     if (v == 32 || v == 64 || v == 128 || v == 192 || v == 256) h->group = v;
+    if (v == vk::GROUP_TILE && vk::tile_warps_for(N) > 0) h->group = v;
   }
-  const size_t need = vk::smem_bytes_per_filter(N) * ((h->group >= 128 ? h->group : 128) / h->group);
+  const size_t need = (h->group == vk::GROUP_TILE) ? vk::tile_smem_bytes(N)
+                                                   : vk::smem_bytes_per_filter(N) * ((h->group >= 128 ? h->group : 128) / h->group);
   if (need > (size_t)prop.sharedMemPerBlockOptin) {
     delete h;
     return fail(VIEKF_ERR_UNSUPPORTED, "viekf_batch_create: N too large for the shared-memory resident covariance");

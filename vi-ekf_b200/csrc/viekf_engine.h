@@ -60,8 +60,13 @@ struct KParams {
   int32_t n_buckets;
 };
 
-// threads cooperating on one filter, chosen from N
+// threads cooperating on one filter, chosen from N; GROUP_TILE selects the register-tile executor (viekf_tile.cu)
+static const int GROUP_TILE = 1;
 int group_size_for(int N);
+// register-tile executor: tile warps for N (0 = N outside its range), shared memory per filter, launch
+int tile_warps_for(int N);
+size_t tile_smem_bytes(int N);
+cudaError_t launch_tile(const KParams& p, int sm_count, cudaStream_t stream);
 // dynamic shared memory (bytes) one filter needs
 size_t smem_bytes_per_filter(int N);
 // launches the tape executor; grid sized as a multiple of the SM count. Returns cudaError_t.

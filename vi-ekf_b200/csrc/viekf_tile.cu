@@ -1,0 +1,1001 @@
+// viekf_tile.cu -- register-tile tape executor of the VI-EKF batch engine (sm_100a, FP64).
+//
+// Same contract as viekf_kernel.cu (one thread group owns one filter for a whole tape slice; events in order; HBM layout of
+// x / packed P unchanged), different placement of the covariance on chip:
+//
+//   P_ff (feature-feature, the O(N^2) part)  lives in REGISTERS: the lower block-triangle of 2x2-feature tiles (6x6 doubles),
+//                                            one tile per thread of the TW "tile warps"; diagonal tiles keep a mirrored copy
+//   P_bb (16x16, full symmetric), P_fb (3N x 16)  live in shared memory and are owned by the last ("base") warp
+//
+// so the two O(N^2) loops of the filter -- the structured A_d P A_d^T of propagate_state (vi_ekf.cpp:302-304) and the
+// Joseph / partial covariance update (vi_ekf_meas.cpp:254-265) -- run as fully unrolled FP64 FMA streams on register
+// operands; shared memory only supplies the O(N) row / column vectors, mostly as warp broadcasts.  Feature removal
+// (clear_feature / keep_only_features, vi_ekf_feat.cpp:50-142) reshuffles the tiles through the filter's own packed P in
+// global memory (L2 round trip), which is also the load / store path at the ends of a slice.
+//
+// Padding: with `len` live features the tile grid covers lenp = len rounded up to even; every quantity of the padding
+// feature (A_d rows, G_d rows, Y rows, P_fb rows, update vectors, tile entries) is an exact zero, so no per-element guards
+// are needed inside the unrolled loops.
+#include "viekf_dev.cuh"
+
+namespace vk {
+
+constexpr int PBS = 18;  // row stride of P_bb: even (16-byte rows for vector loads), 2-way conflicts at worst for row-per-lane access
+
+struct TLayout {
+  int x, Pbb, Pfb, Pfb2, lam, dx, Abd, AbT, T, Ac, Gb, Afd, Gd, Y, upd, small, ids, smap, total, TR;
+};
+__host__ __device__ inline TLayout make_tlayout(int N) {
+  TLayout L;
+  L.TR = (N + 1) / 2;
+  const int NP = 2 * L.TR;
+  const int nmaxp = 16 + 3 * NP;
+  int o = 0;
+  L.x = o;     o += ev2(17 + 5 * N);
+  L.Pbb = o;   o += 16 * PBS;           // full symmetric 16 x 16, row stride PBS
+  L.Pfb = o;   o += ev2(3 * NP * 17);   // [feature row][17]: base columns 0..15, stride 17 (conflict-free row-per-lane access)
+  L.Pfb2 = o;  o += ev2(3 * NP * 17);   // second buffer: propagate and compaction write here, then the two are swapped
+  L.lam = o;   o += ev2(nmaxp);
+  L.dx = o;    o += ev2(nmaxp);
+  L.Abd = o;   o += 256;
+  L.AbT = o;   o += 256;
+  L.T = o;     o += 256;
+  L.Ac = o;    o += 144;
+  L.Gb = o;    o += 54 + 2;
+  L.Afd = o;   o += ev2(3 * NP * 19);
+  L.Gd = o;    o += ev2(nmaxp * 6);
+  L.Y = o;     o += ev2(3 * NP * 17 > 27 * N ? 3 * NP * 17 : 27 * N);
+  L.upd = L.Afd;
+  const int upd_end = L.upd + ev2(10 * nmaxp);
+  if (upd_end > o) o = upd_end;
+  L.small = o; o += 80;
+  L.ids = o;   o += ev2(N + 12);
+  L.smap = o;  o += ev2(NP / 2 + 2);
+  L.total = ev2(o);
+  return L;
+}
+
+size_t tile_smem_bytes(int N) { return (size_t)make_tlayout(N).total * sizeof(double); }
+
+template <int TW>
+struct TCtx : Ctx<32 * (TW + 1)> {
+  double *Pbb, *Pfb, *Pfb2;
+  int* smap;
+  int ti, tj;   // tile coordinates in units of 2 features, ti >= tj
+  bool tile;    // this thread owns a tile of the (capacity) grid
+  bool basew;   // this thread belongs to the base warp
+  int lane;
+};
+
+#define PT(r, c) Pt[(r) * 6 + (c)]
+
+template <int TW>
+__device__ __forceinline__ void tile_mirror(const TCtx<TW>& c, double (&Pt)[36]) {
+  if (c.tile && c.ti == c.tj) {
+#pragma unroll
+    for (int r = 0; r < 6; r++)
+#pragma unroll
+      for (int cc = r + 1; cc < 6; cc++) PT(r, cc) = PT(cc, r);
+  }
+}
+
+// tiles <- packed P in global memory; new feature f comes from old feature smap[f] (identity when !use_map); dead blocks = 0
+template <int TW>
+__device__ __forceinline__ void tile_load(const TCtx<TW>& c, const double* gP, double (&Pt)[36], int len, bool use_map) {
+#pragma unroll
+  for (int bi = 0; bi < 2; bi++)
+#pragma unroll
+    for (int bj = 0; bj < 2; bj++) {
+      const int fi = 2 * c.ti + bi, fj = 2 * c.tj + bj;
+      const bool live = c.tile && fi < len && fj < len;
+      int oi = fi, oj = fj;
+      if (live && use_map) {
+        oi = c.smap[fi];
+        oj = c.smap[fj];
+      }
+#pragma unroll
+      for (int rr = 0; rr < 3; rr++)
+#pragma unroll
+        for (int cc = 0; cc < 3; cc++) {
+          double v = 0.0;
+          if (live) v = __ldcg(gP + psym(16 + 3 * oi + rr, 16 + 3 * oj + cc));
+          PT(3 * bi + rr, 3 * bj + cc) = v;
+        }
+    }
+}
+
+// packed P in global memory <- tiles (lower triangle of the live part only)
+template <int TW>
+__device__ __forceinline__ void tile_store(const TCtx<TW>& c, double* gP, const double (&Pt)[36], int len) {
+#pragma unroll
+  for (int bi = 0; bi < 2; bi++)
+#pragma unroll
+    for (int bj = 0; bj < 2; bj++) {
+      const int fi = 2 * c.ti + bi, fj = 2 * c.tj + bj;
+      const bool live = c.tile && fi < len && fj < len && fi >= fj;
+      if (live) {
+#pragma unroll
+        for (int rr = 0; rr < 3; rr++)
+#pragma unroll
+          for (int cc = 0; cc < 3; cc++)
+            if (fi > fj || rr >= cc) gP[plo(16 + 3 * fi + rr, 16 + 3 * fj + cc)] = PT(3 * bi + rr, 3 * bj + cc);
+      }
+    }
+}
+
+// fix_depth (vi_ekf_helper.cpp:128-156): the thread that owns the diagonal tile handles its two features
+template <int TW>
+__device__ __forceinline__ void tile_fix_depth(const TCtx<TW>& c, const KParams& p, double (&Pt)[36], int len) {
+  if (!(c.tile && c.ti == c.tj)) return;
+#pragma unroll
+  for (int bi = 0; bi < 2; bi++) {
+    const int i = 2 * c.ti + bi;
+    if (i >= len) continue;
+    double* rho = c.x + 17 + 5 * i + 4;
+    const double reset = 1.0 / (2.0 * p.min_depth);
+    double r = *rho;
+    uint32_t fl = 0;
+    int nfix = 0;
+    if (r != r) {
+      r = reset;
+      fl |= VIEKF_FLAG_DEPTH_NAN_FIXED;
+      nfix++;
+    }
+    if (r < 0.0) {
+      const double err = reset - r;
+      PT(3 * bi + 2, 3 * bi + 2) += err * err;
+      r = reset;
+      fl |= VIEKF_FLAG_DEPTH_NEG_FIXED;
+      nfix++;
+    } else if (r > 1e2) {
+      PT(3 * bi + 2, 3 * bi + 2) = p.P0f[2];
+      r = reset;
+      fl |= VIEKF_FLAG_DEPTH_BIG_FIXED;
+      nfix++;
+    }
+    if (nfix) {
+      *rho = r;
+      atomicOr((unsigned*)&c.sc[SC_FLAGS], fl);
+      atomicAdd(&c.sc[SC_NFIX], nfix);
+    }
+  }
+}
+
+// ------------------------------------------------------------------------------------------------------------------
+// PROP: propagate_state (vi_ekf.cpp:262-318) with the structured covariance product
+// ------------------------------------------------------------------------------------------------------------------
+template <int TW>
+__device__ __forceinline__ void tile_propagate(TCtx<TW>& c, const KParams& p, const viekf_event& E, double (&Pt)[36]) {
+  constexpr int G = 32 * (TW + 1);
+  double dt;
+  int len;
+  if (!prop_discretise(c, p, E, dt, len, 1)) return;
+  const int lenp = (len + 1) & ~1;
+  const int nfr = 3 * lenp;
+  // ---- phase C: one row of Y = A_fb P_bb + A_ff P_fb (3 lenp x 16) or of T = A_bb P_bb per thread ----
+  for (int task = c.tid; task < nfr + 16; task += G) {
+    double acc[16];
+#pragma unroll
+    for (int q = 0; q < 16; q++) acc[q] = 0.0;
+    if (task < nfr) {
+      const int fr = task, i = fr / 3;
+      const double* Ad = c.Afd + fr * 19;
+#pragma unroll
+      for (int k = 3; k < 16; k++) {
+        const double a = Ad[k];
+        const double2* row = (const double2*)(c.Pbb + k * PBS);
+#pragma unroll
+        for (int q = 0; q < 8; q++) {
+          const double2 v = row[q];
+          acc[2 * q] = fma(a, v.x, acc[2 * q]);
+          acc[2 * q + 1] = fma(a, v.y, acc[2 * q + 1]);
+        }
+      }
+#pragma unroll
+      for (int k = 0; k < 3; k++) {
+        const double a = Ad[16 + k];
+        const double* row = c.Pfb + (3 * i + k) * 17;
+#pragma unroll
+        for (int q = 0; q < 16; q++) acc[q] = fma(a, row[q], acc[q]);
+      }
+      double* Yr = c.Y + fr * 17;
+#pragma unroll
+      for (int q = 0; q < 16; q++) Yr[q] = acc[q];
+    } else {
+      const int r = task - nfr;
+#pragma unroll
+      for (int k = 0; k < 16; k++) {
+        const double a = c.Abd[r * 16 + k];
+        const double2* row = (const double2*)(c.Pbb + k * PBS);
+#pragma unroll
+        for (int q = 0; q < 8; q++) {
+          const double2 v = row[q];
+          acc[2 * q] = fma(a, v.x, acc[2 * q]);
+          acc[2 * q + 1] = fma(a, v.y, acc[2 * q + 1]);
+        }
+      }
+#pragma unroll
+      for (int q = 0; q < 16; q++) c.T[r * 16 + q] = acc[q];
+    }
+  }
+  c.sync();
+  // ---- phase D: state boxplus; P'_ff tiles in registers; base warp: P'_bb in place (T holds A_bb P_bb), P'_fb into Pfb2 ----
+  boxplus_inplace(c, c.dx, dt, len);
+  if (c.tid == 0) *c.tcur = E.t;
+  if (c.tile && 2 * c.ti < len) {
+    const int R = 6 * c.ti, C = 6 * c.tj;
+    // Z = A_ff,i P_ij  (block rows), in place
+#pragma unroll
+    for (int bi = 0; bi < 2; bi++) {
+      double Af[9];
+#pragma unroll
+      for (int a = 0; a < 3; a++)
+#pragma unroll
+        for (int k = 0; k < 3; k++) Af[a * 3 + k] = c.Afd[(R + 3 * bi + a) * 19 + 16 + k];
+#pragma unroll
+      for (int cc = 0; cc < 6; cc++) {
+        const double t0 = PT(3 * bi, cc), t1 = PT(3 * bi + 1, cc), t2 = PT(3 * bi + 2, cc);
+#pragma unroll
+        for (int a = 0; a < 3; a++) PT(3 * bi + a, cc) = fma(Af[a * 3 + 2], t2, fma(Af[a * 3 + 1], t1, Af[a * 3] * t0));
+      }
+    }
+    // Z += A_fb,i P_bf,j   (base columns VEL..MU: 3..15)
+#pragma unroll
+    for (int k = 3; k < 16; k++) {
+      double ar[6], bc[6];
+#pragma unroll
+      for (int r = 0; r < 6; r++) ar[r] = c.Afd[(R + r) * 19 + k];
+#pragma unroll
+      for (int cc = 0; cc < 6; cc++) bc[cc] = c.Pfb[(C + cc) * 17 + k];
+#pragma unroll
+      for (int r = 0; r < 6; r++)
+#pragma unroll
+        for (int cc = 0; cc < 6; cc++) PT(r, cc) = fma(ar[r], bc[cc], PT(r, cc));
+    }
+    // O = Z A_ff,j^T  (block columns), in place
+#pragma unroll
+    for (int bj = 0; bj < 2; bj++) {
+      double Af[9];
+#pragma unroll
+      for (int b = 0; b < 3; b++)
+#pragma unroll
+        for (int k = 0; k < 3; k++) Af[b * 3 + k] = c.Afd[(C + 3 * bj + b) * 19 + 16 + k];
+#pragma unroll
+      for (int r = 0; r < 6; r++) {
+        const double t0 = PT(r, 3 * bj), t1 = PT(r, 3 * bj + 1), t2 = PT(r, 3 * bj + 2);
+#pragma unroll
+        for (int b = 0; b < 3; b++) PT(r, 3 * bj + b) = fma(t2, Af[b * 3 + 2], fma(t1, Af[b * 3 + 1], t0 * Af[b * 3]));
+      }
+    }
+    // O += Y_i A_fb,j^T
+#pragma unroll
+    for (int k = 3; k < 16; k++) {
+      double yr[6], ac[6];
+#pragma unroll
+      for (int r = 0; r < 6; r++) yr[r] = c.Y[(R + r) * 17 + k];
+#pragma unroll
+      for (int cc = 0; cc < 6; cc++) ac[cc] = c.Afd[(C + cc) * 19 + k];
+#pragma unroll
+      for (int r = 0; r < 6; r++)
+#pragma unroll
+        for (int cc = 0; cc < 6; cc++) PT(r, cc) = fma(yr[r], ac[cc], PT(r, cc));
+    }
+    // O += G_d,i Qu G_d,j^T
+#pragma unroll
+    for (int q = 0; q < 6; q++) {
+      double gr[6], gc[6];
+      const double qu = p.Qu[q];
+#pragma unroll
+      for (int r = 0; r < 6; r++) gr[r] = c.Gd[(16 + R + r) * 6 + q] * qu;
+#pragma unroll
+      for (int cc = 0; cc < 6; cc++) gc[cc] = c.Gd[(16 + C + cc) * 6 + q];
+#pragma unroll
+      for (int r = 0; r < 6; r++)
+#pragma unroll
+        for (int cc = 0; cc < 6; cc++) PT(r, cc) = fma(gr[r], gc[cc], PT(r, cc));
+    }
+    if (c.ti == c.tj) {
+#pragma unroll
+      for (int bi = 0; bi < 2; bi++)
+        if (2 * c.ti + bi < len) {
+#pragma unroll
+          for (int a = 0; a < 3; a++) PT(3 * bi + a, 3 * bi + a) += p.Qxf[a];
+        }
+    }
+    tile_mirror(c, Pt);
+  }
+  if (c.basew) {
+    // P'_bb = T A_bb^T + G_d Qu G_d^T + Qx: lower triangle, mirrored
+    for (int e = c.lane; e < 136; e += 32) {
+      int r = (int)((sqrtf(8.0f * (float)e + 1.0f) - 1.0f) * 0.5f);
+      while (((r + 1) * (r + 2) >> 1) <= e) r++;
+      while (((r * (r + 1)) >> 1) > e) r--;
+      const int cc = e - ((r * (r + 1)) >> 1);
+      double s = 0;
+#pragma unroll
+      for (int k = 0; k < 16; k++) s = fma(c.T[r * 16 + k], c.Abd[cc * 16 + k], s);
+#pragma unroll
+      for (int q = 0; q < 6; q++) s = fma(c.Gd[r * 6 + q] * p.Qu[q], c.Gd[cc * 6 + q], s);
+      if (r == cc) s += p.Qx[r];
+      c.Pbb[r * PBS + cc] = s;
+      c.Pbb[cc * PBS + r] = s;
+    }
+    // P'_fb = Y A_bb^T + G_d,f Qu G_d,b^T: lane = (row parity, base column)
+    const int cc = c.lane & 15;
+    double abt[16], gq[6];
+#pragma unroll
+    for (int k = 0; k < 16; k++) abt[k] = c.AbT[k * 16 + cc];
+#pragma unroll
+    for (int q = 0; q < 6; q++) gq[q] = c.Gd[cc * 6 + q] * p.Qu[q];
+#pragma unroll 2
+    for (int fr = (c.lane >> 4); fr < nfr; fr += 2) {
+      const double* Yr = c.Y + fr * 17;
+      const double* Gr = c.Gd + (16 + fr) * 6;
+      double s0 = 0, s1 = 0;
+#pragma unroll
+      for (int k = 0; k < 16; k += 2) {
+        s0 = fma(Yr[k], abt[k], s0);
+        s1 = fma(Yr[k + 1], abt[k + 1], s1);
+      }
+#pragma unroll
+      for (int q = 0; q < 6; q += 2) {
+        s0 = fma(Gr[q], gq[q], s0);
+        s1 = fma(Gr[q + 1], gq[q + 1], s1);
+      }
+      c.Pfb2[fr * 17 + cc] = s0 + s1;
+    }
+  }
+  c.sync();
+  {
+    double* t = c.Pfb;
+    c.Pfb = c.Pfb2;
+    c.Pfb2 = t;
+  }
+  // ---- phase F: fix_depth ----
+  tile_fix_depth(c, p, Pt, len);
+}
+
+// ------------------------------------------------------------------------------------------------------------------
+// UPD: VIEKF::update (vi_ekf_meas.cpp:196-278) as a symmetric rank update
+//   P_ij += (1 - a_i a_j) ( W_i.K_j - K_i.H_j ),   H = P H^T,  K = H S^-1,  W = K S - H,  a = 1 - lambda (partial update) or 0
+// which is the Joseph form (I-KH) P (I-KH)^T + K R K^T - P = K S K^T - K (HP) - (HP)^T K^T with the two terms that share
+// K_j merged.  Vectors live in the update workspace (padding rows are exact zeros).
+// ------------------------------------------------------------------------------------------------------------------
+struct TUpdVec {
+  double2 *Kv, *Hv, *Wv;
+  double *K2, *H2, *W2, *av;
+  __device__ __forceinline__ TUpdVec(double* w, int nmaxp) {
+    Kv = (double2*)w;
+    Hv = (double2*)(w + 2 * nmaxp);
+    Wv = (double2*)(w + 4 * nmaxp);
+    K2 = w + 6 * nmaxp;
+    H2 = w + 7 * nmaxp;
+    W2 = w + 8 * nmaxp;
+    av = w + 9 * nmaxp;
+  }
+};
+
+template <int RD>
+__device__ __forceinline__ double rank_delta(double2 wr, double2 kr, double w2r, double k2r, double2 kc, double2 hc, double k2c, double h2c) {
+  double d = wr.x * kc.x;
+  d = fma(-kr.x, hc.x, d);
+  if (RD >= 2) {
+    d = fma(wr.y, kc.y, d);
+    d = fma(-kr.y, hc.y, d);
+  }
+  if (RD == 3) {
+    d = fma(w2r, k2c, d);
+    d = fma(-k2r, h2c, d);
+  }
+  return d;
+}
+
+template <int TW, int RD, int MC>
+__device__ __forceinline__ int tile_update_core(TCtx<TW>& c, const KParams& p, const viekf_event& E, int n, int len, const HReg<RD, MC>& H,
+                                                double (&Pt)[36]) {
+  constexpr int G = 32 * (TW + 1);
+  int* cols = c.sc + SC_COUNT;
+  const int lenp = (len + 1) & ~1;
+  const int npad = 16 + 3 * lenp;
+  TUpdVec v(c.upd, 16 + 3 * ((p.N + 1) & ~1));
+  const bool featcols = (H.m > 0) && (H.col[0] >= 16);  // every H touches either base columns or the columns of one feature
+  // ---- P H^T ----
+  if (!featcols) {
+    for (int i = c.tid; i < npad; i += G) {
+      double s[3] = {0, 0, 0};
+#pragma unroll
+      for (int k = 0; k < MC; k++)
+        if (k < H.m) {
+          const double pv = (i < 16) ? c.Pbb[i * PBS + H.col[k]] : c.Pfb[(i - 16) * 17 + H.col[k]];
+#pragma unroll
+          for (int a = 0; a < RD; a++) s[a] = fma(pv, H.h[a * MC + k], s[a]);
+        }
+      v.Hv[i] = make_double2(s[0], s[1]);
+      if (RD == 3) v.H2[i] = s[2];
+    }
+  } else {
+    const int fi = (H.col[0] - 16) / 3, tb = fi >> 1, sb = fi & 1;
+    // effective 3-column Jacobian of the feature block: he[a][kk] = sum over the k with local column kk
+    double he[RD][3];
+#pragma unroll
+    for (int a = 0; a < RD; a++)
+#pragma unroll
+      for (int kk = 0; kk < 3; kk++) he[a][kk] = 0.0;
+#pragma unroll
+    for (int k = 0; k < MC; k++)
+      if (k < H.m) {
+        const int lk = H.col[k] - 16 - 3 * fi;
+#pragma unroll
+        for (int a = 0; a < RD; a++)
+#pragma unroll
+          for (int kk = 0; kk < 3; kk++)
+            if (lk == kk) he[a][kk] += H.h[a * MC + k];
+      }
+    if (c.basew && c.lane < 16) {
+      const int i = c.lane;
+      double s[3] = {0, 0, 0};
+#pragma unroll
+      for (int kk = 0; kk < 3; kk++) {
+        const double pv = c.Pfb[(3 * fi + kk) * 17 + i];
+#pragma unroll
+        for (int a = 0; a < RD; a++) s[a] = fma(pv, he[a][kk], s[a]);
+      }
+      v.Hv[i] = make_double2(s[0], s[1]);
+      if (RD == 3) v.H2[i] = s[2];
+    }
+    if (c.tile && 2 * c.ti < len) {
+      if (c.tj == tb) {  // rows of this tile against the columns of feature fi
+#pragma unroll
+        for (int r = 0; r < 6; r++) {
+          double s[3] = {0, 0, 0};
+#pragma unroll
+          for (int kk = 0; kk < 3; kk++) {
+            const double pv = sb ? PT(r, 3 + kk) : PT(r, kk);
+#pragma unroll
+            for (int a = 0; a < RD; a++) s[a] = fma(pv, he[a][kk], s[a]);
+          }
+          v.Hv[16 + 6 * c.ti + r] = make_double2(s[0], s[1]);
+          if (RD == 3) v.H2[16 + 6 * c.ti + r] = s[2];
+        }
+      } else if (c.ti == tb) {  // columns of this tile against the rows of feature fi (symmetry)
+#pragma unroll
+        for (int cc = 0; cc < 6; cc++) {
+          double s[3] = {0, 0, 0};
+#pragma unroll
+          for (int kk = 0; kk < 3; kk++) {
+            const double pv = sb ? PT(3 + kk, cc) : PT(kk, cc);
+#pragma unroll
+            for (int a = 0; a < RD; a++) s[a] = fma(pv, he[a][kk], s[a]);
+          }
+          v.Hv[16 + 6 * c.tj + cc] = make_double2(s[0], s[1]);
+          if (RD == 3) v.H2[16 + 6 * c.tj + cc] = s[2];
+        }
+      }
+    }
+  }
+  if (c.tid == 0) cols[8] = H.hnan ? 1 : 0;
+  c.sync();
+  // ---- S = H P H^T + R, S^-1, Mahalanobis gate: every thread evaluates the same registers ----
+  double S[3][3], Si[3][3];
+  {
+    double ph[MC][3];
+#pragma unroll
+    for (int k = 0; k < MC; k++) {
+      const int ck = (k < H.m) ? H.col[k] : 0;
+      const double2 t = v.Hv[ck];
+      ph[k][0] = t.x;
+      ph[k][1] = t.y;
+      ph[k][2] = (RD == 3) ? v.H2[ck] : 0.0;
+    }
+#pragma unroll
+    for (int a = 0; a < RD; a++)
+#pragma unroll
+      for (int b = 0; b < RD; b++) {
+        double s = 0;
+#pragma unroll
+        for (int k = 0; k < MC; k++)
+          if (k < H.m) s += H.h[a * MC + k] * ph[k][b];
+        S[a][b] = s + E.R[a + b * RD];
+      }
+  }
+  const double mahal = inverse_and_mahal<RD>(S, Si, H.res);
+  if (mahal > 9.0) {
+    if (c.tid == 0) c.sc[SC_NGATED] += 1;
+    return VIEKF_MEAS_GATED;  // early return: no fix_depth (vi_ekf_meas.cpp:238)
+  }
+  // ---- K = P H^T S^-1, W = K S - P H^T, state correction lambda o (K r) ----
+  bool bad = false;
+  for (int i = c.tid; i < npad; i += G) {
+    const double2 h01 = v.Hv[i];
+    double ph[3] = {h01.x, h01.y, 0.0};
+    if (RD == 3) ph[2] = v.H2[i];
+    double k3[3] = {0, 0, 0}, w3[3] = {0, 0, 0};
+#pragma unroll
+    for (int b = 0; b < RD; b++) {
+      double s = 0;
+#pragma unroll
+      for (int a = 0; a < RD; a++) s += ph[a] * Si[a][b];
+      k3[b] = s;
+      bad |= (s != s);
+    }
+    double d = 0;
+#pragma unroll
+    for (int a = 0; a < RD; a++) d += k3[a] * H.res[a];
+#pragma unroll
+    for (int a = 0; a < RD; a++) {
+      double s = 0;
+#pragma unroll
+      for (int b = 0; b < RD; b++) s += k3[b] * S[b][a];
+      w3[a] = s - ph[a];
+    }
+    v.Kv[i] = make_double2(k3[0], k3[1]);
+    v.Wv[i] = make_double2(w3[0], w3[1]);
+    if (RD == 3) {
+      v.K2[i] = k3[2];
+      v.W2[i] = w3[2];
+    }
+    const double li = c.lam[i];
+    v.av[i] = p.use_partial ? 1.0 - li : 0.0;
+    c.dx[i] = p.use_partial ? li * d : d;
+  }
+  if (bad) atomicOr((unsigned*)&cols[8], 1u);
+  c.sync();
+  if (!cols[8]) {
+    boxplus_inplace(c, c.dx, 1.0, len);
+    if (c.tile && 2 * c.ti < len) {
+      const int R = 16 + 6 * c.ti, C = 16 + 6 * c.tj;
+      double2 kc[6], hc[6];
+      double ac[6], k2c[6], h2c[6];
+#pragma unroll
+      for (int cc = 0; cc < 6; cc++) {
+        kc[cc] = v.Kv[C + cc];
+        hc[cc] = v.Hv[C + cc];
+        ac[cc] = v.av[C + cc];
+        k2c[cc] = (RD == 3) ? v.K2[C + cc] : 0.0;
+        h2c[cc] = (RD == 3) ? v.H2[C + cc] : 0.0;
+      }
+#pragma unroll
+      for (int r = 0; r < 6; r++) {
+        const double2 wr = v.Wv[R + r], kr = v.Kv[R + r];
+        const double ar = v.av[R + r];
+        const double w2r = (RD == 3) ? v.W2[R + r] : 0.0, k2r = (RD == 3) ? v.K2[R + r] : 0.0;
+#pragma unroll
+        for (int cc = 0; cc < 6; cc++) {
+          const double d = rank_delta<RD>(wr, kr, w2r, k2r, kc[cc], hc[cc], k2c[cc], h2c[cc]);
+          const double u = fma(-ar, ac[cc], 1.0);
+          PT(r, cc) = fma(d, u, PT(r, cc));
+        }
+      }
+      tile_mirror(c, Pt);
+    }
+    if (c.basew) {
+      // rows of [P_bb; P_fb]: one row per lane, three rows per pass; column vectors are warp broadcasts
+      constexpr int NR = 3;
+      for (int ib = c.lane; ib < npad; ib += 32 * NR) {
+        double2 wr[NR], kr[NR];
+        double ar[NR], w2r[NR], k2r[NR];
+        double* prow[NR];
+        int jmax[NR], ii[NR];
+#pragma unroll
+        for (int m = 0; m < NR; m++) {
+          const int i = ib + 32 * m;
+          const bool valid = i < npad;
+          ii[m] = valid ? i : 0;
+          wr[m] = v.Wv[ii[m]];
+          kr[m] = v.Kv[ii[m]];
+          ar[m] = v.av[ii[m]];
+          w2r[m] = (RD == 3) ? v.W2[ii[m]] : 0.0;
+          k2r[m] = (RD == 3) ? v.K2[ii[m]] : 0.0;
+          prow[m] = (ii[m] < 16) ? c.Pbb + ii[m] * PBS : c.Pfb + (ii[m] - 16) * 17;
+          jmax[m] = valid ? (ii[m] < 16 ? ii[m] : 15) : -1;
+        }
+#pragma unroll 4
+        for (int j = 0; j < 16; j++) {
+          const double2 kj = v.Kv[j], hj = v.Hv[j];
+          const double aj = v.av[j];
+          const double k2j = (RD == 3) ? v.K2[j] : 0.0, h2j = (RD == 3) ? v.H2[j] : 0.0;
+#pragma unroll
+          for (int m = 0; m < NR; m++)
+            if (j <= jmax[m]) {
+              const double d = rank_delta<RD>(wr[m], kr[m], w2r[m], k2r[m], kj, hj, k2j, h2j);
+              const double u = fma(-ar[m], aj, 1.0);
+              const double nv = fma(d, u, prow[m][j]);
+              prow[m][j] = nv;
+              if (ii[m] < 16) c.Pbb[j * PBS + ii[m]] = nv;
+            }
+        }
+      }
+    }
+  } else if (c.tid == 0) {
+    c.sc[SC_FLAGS] |= VIEKF_FLAG_NAN_GAIN;
+    c.sc[SC_NNAN] += 1;
+  }
+  c.sync();
+  tile_fix_depth(c, p, Pt, len);
+  return VIEKF_MEAS_SUCCESS;
+}
+
+// ------------------------------------------------------------------------------------------------------------------
+// feature management
+// ------------------------------------------------------------------------------------------------------------------
+// init_feature (vi_ekf_feat.cpp:6-47).  Returns (uniformly) whether a slot was available.
+template <int TW>
+__device__ __forceinline__ bool tile_init_feature(TCtx<TW>& c, const KParams& p, double l0, double l1, double depth, double (&Pt)[36]) {
+  constexpr int G = 32 * (TW + 1);
+  const int len = c.sc[SC_LEN];
+  if (len >= p.N) return false;
+  c.sync();
+  if (c.tid == 0) {
+    const double lc0 = l0 - p.cc[0], lc1 = l1 - p.cc[1];
+    V3 z = mk3(lc0, lc1 * (p.fl[1] / p.fl[0]), p.fl[0]);
+    const double nz = norm(z);
+    z = mk3(z.x / nz, z.y / nz, z.z / nz);
+    Q4 q = from_two_unit_vectors(mk3(0, 0, 1), z);
+    double d = depth;
+    if (d != d) d = 2.0 * p.min_depth;
+    double* xf = c.x + 17 + 5 * len;
+    stq(xf, q);
+    xf[4] = 1.0 / d;
+    c.ids[len] = c.sc[SC_NEXT];
+    c.sc[SC_NEXT] += 1;
+    c.sc[SC_LEN] = len + 1;
+  }
+  // covariance: rows / columns of the new feature (and of the padding feature that shares its tile row) zero, P0_feat on the diagonal
+  const int tb = len >> 1, sb = len & 1;
+  if (c.tile && c.ti == tb) {
+#pragma unroll
+    for (int r = 0; r < 6; r++)
+#pragma unroll
+      for (int cc = 0; cc < 6; cc++)
+        if (sb == 0 || r >= 3 || (c.tj == tb && cc >= 3)) PT(r, cc) = 0.0;
+    if (c.tj == tb) {
+#pragma unroll
+      for (int k = 0; k < 3; k++) {
+        if (sb)
+          PT(3 + k, 3 + k) = p.P0f[k];
+        else
+          PT(k, k) = p.P0f[k];
+      }
+    }
+  }
+  {
+    const int r0 = 3 * len, r1 = 3 * ((len + 2) & ~1);  // through the end of the tile row
+    for (int e = c.tid; e < (r1 - r0) * 16; e += G) c.Pfb[(r0 + (e >> 4)) * 17 + (e & 15)] = 0.0;
+  }
+  c.sync();
+  return true;
+}
+
+// Order-preserving removal of features: new feature f <- old feature smap[f], f < newlen (clear_feature, vi_ekf_feat.cpp:50-73,
+// applied once for all removals).  Tiles go through the filter's packed P in global memory; x, ids and P_fb through registers
+// and the second P_fb buffer.  Precondition: smap[] published by a barrier.
+template <int TW>
+__device__ __forceinline__ void tile_compact(TCtx<TW>& c, const KParams& p, int len, int newlen, double (&Pt)[36]) {
+  constexpr int G = 32 * (TW + 1);
+  double* gP = p.P + c.b * p.ps;
+  tile_store(c, gP, Pt, len);
+  double xf[5];
+  int idv = 0;
+  if (c.tid < newlen) {
+    const int src = c.smap[c.tid];
+#pragma unroll
+    for (int k = 0; k < 5; k++) xf[k] = c.x[17 + 5 * src + k];
+    idv = c.ids[src];
+  }
+  const int newp = (newlen + 1) & ~1;
+  for (int e = c.tid; e < 3 * newp * 16; e += G) {
+    const int fr = e >> 4, cc = e & 15, f = fr / 3;
+    c.Pfb2[fr * 17 + cc] = (f < newlen) ? c.Pfb[(3 * c.smap[f] + (fr - 3 * f)) * 17 + cc] : 0.0;
+  }
+  c.sync();
+  if (c.tid < newlen) {
+#pragma unroll
+    for (int k = 0; k < 5; k++) c.x[17 + 5 * c.tid + k] = xf[k];
+    c.ids[c.tid] = idv;
+  }
+  {
+    double* t = c.Pfb;
+    c.Pfb = c.Pfb2;
+    c.Pfb2 = t;
+  }
+  tile_load(c, gP, Pt, newlen, true);
+  if (c.tid == 0) c.sc[SC_LEN] = newlen;
+  c.sync();
+}
+
+template <int TW>
+__device__ __forceinline__ void tile_clear_feature(TCtx<TW>& c, const KParams& p, int local, double (&Pt)[36]) {
+  constexpr int G = 32 * (TW + 1);
+  const int len = c.sc[SC_LEN];
+  if (local < 0 || local >= len) return;
+  c.sync();
+  for (int f = c.tid; f < len - 1; f += G) c.smap[f] = f + (f >= local ? 1 : 0);
+  c.sync();
+  tile_compact(c, p, len, len - 1, Pt);
+}
+
+// packed lower triangle of P_bb into the T buffer (idle outside propagate): the statistics and the keyframe-reset pose code
+// read the base block through c.P
+template <int TW>
+__device__ __forceinline__ void tile_pack_base(TCtx<TW>& c) {
+  constexpr int G = 32 * (TW + 1);
+  for (int e = c.tid; e < 256; e += G) {
+    const int r = e >> 4, cc = e & 15;
+    if (cc <= r) c.T[plo(r, cc)] = c.Pbb[r * PBS + cc];
+  }
+  c.P = c.T;
+}
+
+// keyframe_reset (vi_ekf_kfr.cpp:56-157): P = N P N^T, N = I except N(POS,POS) = 0 and the 3x3 attitude block Nb.
+// P_ff is untouched; P_fb gets N^T from the right, P_bb both sides (base warp), then its upper half is re-mirrored.
+template <int TW>
+__device__ __forceinline__ void tile_keyframe_reset(TCtx<TW>& c, const KParams& p) {
+  constexpr int G = 32 * (TW + 1);
+  const int len = c.sc[SC_LEN];
+  c.sync();
+  tile_pack_base(c);
+  c.sync();
+  double* Nb = c.sm + SM_HC;  // 9 doubles, row-major
+  if (c.tid == 0) kfreset_pose(c, p, Nb);
+  c.sync();
+  for (int fr = c.tid; fr < 3 * len; fr += G) {
+    double* row = c.Pfb + fr * 17;
+    double v[3];
+#pragma unroll
+    for (int a = 0; a < 3; a++) {
+      row[a] = 0.0;
+      v[a] = row[6 + a];
+    }
+#pragma unroll
+    for (int a = 0; a < 3; a++) row[6 + a] = Nb[a * 3] * v[0] + Nb[a * 3 + 1] * v[1] + Nb[a * 3 + 2] * v[2];
+  }
+  if (c.basew) {
+    const int l = c.lane;
+    if (l < 16) {  // right factor N^T, one row per lane
+      double* row = c.Pbb + l * PBS;
+      double v[3];
+#pragma unroll
+      for (int a = 0; a < 3; a++) {
+        row[a] = 0.0;
+        v[a] = row[6 + a];
+      }
+#pragma unroll
+      for (int a = 0; a < 3; a++) row[6 + a] = Nb[a * 3] * v[0] + Nb[a * 3 + 1] * v[1] + Nb[a * 3 + 2] * v[2];
+    }
+    __syncwarp();
+    if (l < 16) {  // left factor N, one column per lane
+      double v[3];
+#pragma unroll
+      for (int a = 0; a < 3; a++) {
+        c.Pbb[a * PBS + l] = 0.0;
+        v[a] = c.Pbb[(6 + a) * PBS + l];
+      }
+#pragma unroll
+      for (int a = 0; a < 3; a++) c.Pbb[(6 + a) * PBS + l] = Nb[a * 3] * v[0] + Nb[a * 3 + 1] * v[1] + Nb[a * 3 + 2] * v[2];
+    }
+    __syncwarp();
+    if (l < 16)
+      for (int cc = 0; cc < l; cc++) c.Pbb[cc * PBS + l] = c.Pbb[l * PBS + cc];
+  }
+  c.sync();
+}
+
+// keep_only_features (vi_ekf_feat.cpp:81-142)
+template <int TW>
+__device__ __forceinline__ void tile_keep_only(TCtx<TW>& c, const KParams& p, const int32_t* feats, int nf, double (&Pt)[36]) {
+  constexpr int G = 32 * (TW + 1);
+  c.sync();
+  int* keepf = (int*)c.upd;  // [N] flags, update workspace is idle here
+  if (c.tid == 0) c.sc[SC_TMP1] = 0;
+  c.sync();
+  const int len = c.sc[SC_LEN];
+  const int nkf = c.sc[SC_NKF];
+  {
+    const int32_t* kf = p.kf_ids + c.b * KF_CAP;
+    for (int l = c.tid; l < len; l += G) {
+      const int id = c.ids[l];
+      bool keep = false;
+      for (int i = 0; i < nf; i++) keep |= (feats[i] == id);
+      if (keep && p.use_kfreset) {
+        bool ov = false;
+        for (int j = 0; j < nkf; j++) ov |= (kf[j] == id);
+        if (ov) atomicAdd(&c.sc[SC_TMP1], 1);
+      }
+      keepf[l] = keep ? 1 : 0;
+    }
+  }
+  c.sync();
+  if (c.tid == 0) {
+    int m = 0;
+    for (int l = 0; l < len; l++)
+      if (keepf[l]) c.smap[m++] = l;
+    c.sc[SC_TMP0] = m;
+  }
+  c.sync();
+  const int newlen = c.sc[SC_TMP0];
+  const int overlap = c.sc[SC_TMP1];
+  if (newlen < len) tile_compact(c, p, len, newlen, Pt);
+  const bool reset = p.use_kfreset && nkf > 0 && ((double)overlap / (double)nkf < p.kf_thresh);
+  if (reset) tile_keyframe_reset(c, p);
+  c.sync();  // every thread has taken the (uniform) reset decision from the old list size before thread 0 replaces it
+  if (p.use_kfreset && (reset || nkf == 0)) {
+    int32_t* kf = p.kf_ids + c.b * KF_CAP;
+    const int m = nf < KF_CAP ? nf : KF_CAP;
+    for (int i = c.tid; i < m; i += G) kf[i] = feats[i];
+    if (c.tid == 0) c.sc[SC_NKF] = m;
+  }
+  c.sync();
+}
+
+template <int TW>
+struct TileCore {
+  TCtx<TW>& c;
+  const KParams& p;
+  double (&Pt)[36];
+  template <int RD, int MC>
+  __device__ __forceinline__ int run(const viekf_event& E, int n, int len, const HReg<RD, MC>& H) {
+    return tile_update_core<TW, RD, MC>(c, p, E, n, len, H, Pt);
+  }
+  __device__ __forceinline__ bool init_feature(double l0, double l1, double depth) { return tile_init_feature(c, p, l0, l1, depth, Pt); }
+  __device__ __forceinline__ void fix_depth(int len) { tile_fix_depth(c, p, Pt, len); }
+};
+
+// ------------------------------------------------------------------------------------------------------------------
+// the persistent tape executor, register-tile variant: one CTA of 32 (TW + 1) threads per filter at a time
+// ------------------------------------------------------------------------------------------------------------------
+template <int TW>
+__global__ void __launch_bounds__(32 * (TW + 1), (TW == 3 ? 3 : 1)) viekf_tile_kernel(const __grid_constant__ KParams p) {
+  extern __shared__ __align__(16) double smem[];
+  constexpr int G = 32 * (TW + 1);
+  const TLayout L = make_tlayout(p.N);
+  TCtx<TW> c;
+  c.gi = 0;
+  c.tid = threadIdx.x;
+  c.lane = threadIdx.x & 31;
+  c.basew = (threadIdx.x >> 5) == TW;
+  {
+    const int t = threadIdx.x;
+    int ti = (int)((sqrtf(8.0f * (float)t + 1.0f) - 1.0f) * 0.5f);
+    while (((ti + 1) * (ti + 2) >> 1) <= t) ti++;
+    while (((ti * (ti + 1)) >> 1) > t) ti--;
+    c.ti = ti;
+    c.tj = t - ((ti * (ti + 1)) >> 1);
+    c.tile = !c.basew && ti < L.TR;
+  }
+  double* base = smem;
+  c.x = base + L.x; c.P = base + L.T; c.lam = base + L.lam; c.dx = base + L.dx; c.Abd = base + L.Abd; c.AbT = base + L.AbT; c.T = base + L.T;
+  c.Ac = base + L.Ac; c.Gb = base + L.Gb; c.Afd = base + L.Afd; c.Gd = base + L.Gd; c.Y = base + L.Y; c.upd = base + L.upd;
+  c.Pbb = base + L.Pbb; c.Pfb = base + L.Pfb; c.Pfb2 = base + L.Pfb2;
+  c.sm = base + L.small;
+  c.ids = (int*)(base + L.ids);
+  c.rm = c.ids + p.N;
+  c.sc = c.rm + p.N;
+  c.smap = (int*)(base + L.smap);
+  c.tcur = c.sm + SM_T;
+  const int nmaxp = 16 + 6 * L.TR;
+  for (int i = c.tid; i < nmaxp; i += G) c.lam[i] = (i < 16) ? p.lam[i] : p.lamf[(i - 16) % 3];
+  double Pt[36];
+
+  for (int64_t b = blockIdx.x; b < p.B; b += gridDim.x) {
+    c.b = b;
+    const int64_t ginst = p.inst_off + b;
+    FilterMeta& M = p.meta[b];
+    double* gP = p.P + b * p.ps;
+    // ---- load the filter: meta, ids, live part of x; P_bb / P_fb into shared memory, P_ff into the register tiles ----
+    c.sync();
+    const int len0 = M.len;
+    if (c.tid == 0) {
+      c.sc[SC_LEN] = len0; c.sc[SC_NEXT] = M.next_id; c.sc[SC_STARTED] = M.started; c.sc[SC_FLAGS] = (int)M.flags;
+      c.sc[SC_NGATED] = (int)M.n_gated; c.sc[SC_NFIX] = (int)M.n_fix; c.sc[SC_NNAN] = (int)M.n_nan_gain; c.sc[SC_NKF] = M.n_kf;
+      *c.tcur = M.t;
+      for (int k = 0; k < 6; k++) c.sm[SM_UB + k] = M.ub[k];
+    }
+    for (int i = c.tid; i < len0; i += G) c.ids[i] = p.ids[b * (p.N > 0 ? p.N : 1) + i];
+    {
+      const double* gx = p.x + b * p.xs;
+      const int nx = 17 + 5 * len0;
+      for (int i = c.tid; i < nx; i += G) c.x[i] = gx[i];
+      for (int e = c.tid; e < 256; e += G) {
+        const int r = e >> 4, cc = e & 15;
+        c.Pbb[r * PBS + cc] = gP[psym(r, cc)];
+      }
+      const int nfr0 = 3 * ((len0 + 1) & ~1);
+      for (int e = c.tid; e < nfr0 * 16; e += G) {
+        const int fr = e >> 4, cc = e & 15;
+        c.Pfb[fr * 17 + cc] = (fr < 3 * len0) ? gP[plo(16 + fr, cc)] : 0.0;
+      }
+      tile_load(c, gP, Pt, len0, false);
+    }
+    if (p.ev_count > 0 && c.tid < 8) resolve_values(p, p.ev_first, b, ginst, c.tid, c.sm + SM_ZV);
+    c.sync();
+    // ---- run the tape slice ----
+    for (int64_t e = p.ev_first; e < p.ev_first + p.ev_count; e++) {
+      const viekf_event& E = p.ev[e];
+      const int kind = E.kind;
+      c.zv = c.sm + SM_ZV + 8 * (int)((e - p.ev_first) & 1);
+      if (e + 1 < p.ev_first + p.ev_count && c.tid >= G - 32 && (c.tid & 31) < 8)
+        resolve_values(p, e + 1, b, ginst, c.tid & 31, c.sm + SM_ZV + 8 * (int)((e + 1 - p.ev_first) & 1));
+      int result = VIEKF_MEAS_NONE;
+      switch (kind) {
+        case VIEKF_EV_PROP:
+          tile_propagate(c, p, E, Pt);
+          break;
+        case VIEKF_EV_UPD: {
+          TileCore<TW> core{c, p, Pt};
+          result = ev_update(c, p, E, core);
+          break;
+        }
+        case VIEKF_EV_INIT:
+          result = tile_init_feature(c, p, c.zv[0], c.zv[1], E.z[4], Pt) ? 1 : 0;
+          break;
+        case VIEKF_EV_CLEAR:
+          tile_clear_feature(c, p, find_feature(c, E.id), Pt);
+          break;
+        case VIEKF_EV_KEEP:
+          tile_keep_only(c, p, p.id_pool + E.ids_off, E.n_ids, Pt);
+          break;
+        case VIEKF_EV_KFRESET:
+          tile_keyframe_reset(c, p);
+          break;
+        case VIEKF_EV_STAT:
+          c.sync();
+          tile_pack_base(c);
+          c.sync();
+          ev_stat(c, p, E, ginst);
+          break;
+        default:
+          break;
+      }
+      c.sync();
+      if (p.results && c.tid == 0 && b >= p.res_first && b < p.res_first + p.res_count)
+        p.results[(b - p.res_first) * p.n_events + e] = (uint8_t)result;
+    }
+    // ---- store the filter ----
+    c.sync();
+    const int len1 = c.sc[SC_LEN];
+    if (c.tid == 0) {
+      M.len = len1; M.next_id = c.sc[SC_NEXT]; M.started = c.sc[SC_STARTED]; M.flags = (uint32_t)c.sc[SC_FLAGS];
+      M.n_gated = (uint32_t)c.sc[SC_NGATED]; M.n_fix = (uint32_t)c.sc[SC_NFIX]; M.n_nan_gain = (uint32_t)c.sc[SC_NNAN]; M.n_kf = c.sc[SC_NKF];
+      M.t = *c.tcur;
+      for (int k = 0; k < 6; k++) M.ub[k] = c.sm[SM_UB + k];
+    }
+    for (int i = c.tid; i < len1; i += G) p.ids[b * (p.N > 0 ? p.N : 1) + i] = c.ids[i];
+    {
+      double* gx = p.x + b * p.xs;
+      const int nx = 17 + 5 * len1;
+      for (int i = c.tid; i < nx; i += G) gx[i] = c.x[i];
+      for (int e = c.tid; e < 256; e += G) {
+        const int r = e >> 4, cc = e & 15;
+        if (cc <= r) gP[plo(r, cc)] = c.Pbb[r * PBS + cc];
+      }
+      for (int e = c.tid; e < 3 * len1 * 16; e += G) {
+        const int fr = e >> 4, cc = e & 15;
+        gP[plo(16 + fr, cc)] = c.Pfb[fr * 17 + cc];
+      }
+      tile_store(c, gP, Pt, len1);
+    }
+  }
+}
+
+int tile_warps_for(int N) { return (N >= 7 && N <= 26) ? 3 : 0; }
+
+cudaError_t launch_tile(const KParams& p, int sm_count, cudaStream_t stream) {
+  constexpr int TW = 3;
+  if (tile_warps_for(p.N) != TW) return cudaErrorInvalidValue;
+  const size_t smem = tile_smem_bytes(p.N);
+  cudaError_t e = cudaFuncSetAttribute(viekf_tile_kernel<TW>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  if (e != cudaSuccess) return e;
+  e = cudaFuncSetAttribute(viekf_tile_kernel<TW>, cudaFuncAttributePreferredSharedMemoryCarveout, (int)cudaSharedmemCarveoutMaxShared);
+  if (e != cudaSuccess) return e;
+  int occ = 0;
+  e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, viekf_tile_kernel<TW>, 32 * (TW + 1), smem);
+  if (e != cudaSuccess) return e;
+  if (occ < 1) return cudaErrorInvalidConfiguration;
+  int64_t grid = (int64_t)sm_count * occ;  // persistent: a whole number of waves of the SM count
+  if (p.B < grid) grid = p.B;
+  if (grid < 1) grid = 1;
+  viekf_tile_kernel<TW><<<(unsigned)grid, 32 * (TW + 1), smem, stream>>>(p);
+  return cudaGetLastError();
+}
+
+}  // namespace vk
