@@ -231,23 +231,26 @@ __device__ __forceinline__ void fix_depth_one(const Ctx<G>& c, const KParams& p,
   }
 }
 
-// x <- x [+] d  (vi_ekf_helper.cpp:88-98): base part by the last thread of the group, feature i by thread i
-template <int G>
-__device__ __forceinline__ void boxplus_inplace(const Ctx<G>& c, const double* d, double s, int len) {
-  if (c.tid == G - 1) {
-    double* x = c.x;
+// x <- x [+] d  (vi_ekf_helper.cpp:88-98): base part by thread `base_tid` of the group, feature i by thread i.
+// One out-of-line copy serves propagate and update (instruction-cache footprint).
+static __device__ __noinline__ void boxplus_impl(double* x, const double* d, double s, int len, int tid, int G, int base_tid) {
+  if (tid == base_tid) {
     for (int k = 0; k < 6; k++) x[k] += d[k] * s;
     Q4 q = otimes(ldq(x + 6), qexp(mk3(d[6] * s, d[7] * s, d[8] * s)));
     stq(x + 6, q);
     for (int k = 0; k < 7; k++) x[10 + k] += d[9 + k] * s;
   }
-  for (int i = c.tid; i < len; i += G) {
-    double* xf = c.x + 17 + 5 * i;
+  for (int i = tid; i < len; i += G) {
+    double* xf = x + 17 + 5 * i;
     const double* df = d + 16 + 3 * i;
     Q4 q = qfeat_boxplus(ldq(xf), df[0] * s, df[1] * s);
     stq(xf, q);
     xf[4] += df[2] * s;
   }
+}
+template <int G>
+__device__ __forceinline__ void boxplus_inplace(const Ctx<G>& c, const double* d, double s, int len, int base_tid = G - 1) {
+  boxplus_impl(c.x, d, s, len, c.tid, G, base_tid);
 }
 
 // Guards of propagate_state, continuous dynamics and the discretised rows [A_d | G_d] (phases A, B).  Returns false
@@ -857,20 +860,22 @@ __device__ __forceinline__ double inverse_and_mahal(const double (&S)[3][3], dou
       }
 #pragma unroll
     for (int i = cc + 1; i < RD; i++) {
-      const double f = a[i][cc] / a[cc][cc];
+      const double f = a[i][cc] / a[cc][cc];  // the multiplier keeps the reference's rounding (it decides the pivots that follow)
 #pragma unroll
       for (int j = cc; j < 2 * RD; j++) a[i][j] -= f * a[cc][j];
     }
   }
 #pragma unroll
-  for (int cc = RD - 1; cc >= 0; cc--)
+  for (int cc = RD - 1; cc >= 0; cc--) {
+    const double rp = 1.0 / a[cc][cc];  // one reciprocal per pivot (1 ulp from the reference's RD divisions, far inside 1e-9)
 #pragma unroll
     for (int j = 0; j < RD; j++) {
       double s = a[cc][RD + j];
 #pragma unroll
       for (int k = cc + 1; k < RD; k++) s -= a[cc][k] * a[k][RD + j];
-      a[cc][RD + j] = s / a[cc][cc];
+      a[cc][RD + j] = s * rp;
     }
+  }
   double mahal = 0;
 #pragma unroll
   for (int j = 0; j < RD; j++) {
@@ -885,18 +890,19 @@ __device__ __forceinline__ double inverse_and_mahal(const double (&S)[3][3], dou
   return mahal;
 }
 
-// The measurement Jacobian in registers: RD rows on MC (static) candidate columns, m of them live.
-template <int RD, int MC>
+// The measurement Jacobian in registers: up to 3 rows on 6 (static) candidate columns, m of them live; h[a * 6 + k].
+// One shape for every model keeps a single copy of the update code per residual dimension (instruction-cache footprint).
 struct HReg {
-  double h[RD * MC];
-  int col[MC];
+  double h[18];
+  int col[6];
   int m;
-  double res[RD];
+  double res[3];
   bool hnan;
 };
 
-template <int G, int RD, int MC>
-__device__ int update_core(Ctx<G>& c, const KParams& p, const viekf_event& E, int n, int len, const HReg<RD, MC>& H) {
+template <int G, int RD>
+__device__ int update_core(Ctx<G>& c, const KParams& p, const viekf_event& E, int n, int len, const HReg& H) {
+  constexpr int MC = 6;
   int* cols = c.sc + SC_COUNT;
   UpdVec<G> v(c, 16 + 3 * p.N);
   // ---- P H^T: gather of <= MC columns of P ----
@@ -992,36 +998,34 @@ __device__ int update_core(Ctx<G>& c, const KParams& p, const viekf_event& E, in
 }
 
 // generic path: H, columns and residual were written to shared memory by thread 0
-template <int G, int RD, class Core>
-__device__ __forceinline__ int update_generic(Ctx<G>& c, const KParams& p, const viekf_event& E, int n, int len, Core& core) {
+template <int G>
+__device__ __forceinline__ void load_h_from_smem(Ctx<G>& c, HReg& H) {
   const double* Hc = c.sm + SM_HC;
   const double* res = c.sm + SM_RES;
   const int* cols = c.sc + SC_COUNT;
-  HReg<RD, 6> H;
   H.m = cols[6];
   H.hnan = cols[8] != 0;
 #pragma unroll
   for (int k = 0; k < 6; k++) {
     H.col[k] = cols[k];
 #pragma unroll
-    for (int a = 0; a < RD; a++) H.h[a * 6 + k] = Hc[a * 6 + k];
+    for (int a = 0; a < 3; a++) H.h[a * 6 + k] = Hc[a * 6 + k];
   }
 #pragma unroll
-  for (int a = 0; a < RD; a++) H.res[a] = res[a];
-  c.sync();  // cols[8] is re-armed inside update_core
-  return core.template run<RD, 6>(E, n, len, H);
+  for (int a = 0; a < 3; a++) H.res[a] = res[a];
+  c.sync();  // cols[8] is re-armed inside the update core
 }
 
 // update(meas) with add_measurement's bookkeeping in front (vi_ekf_meas.cpp:130-147,196-278). Returns meas_result_t.
 // The covariance-touching steps are delegated to `core` (SmemCore below: P in shared memory; TileCore in viekf_tile.cu:
-// feature covariance in register tiles), which provides run<RD,MC>(E, n, len, H), init_feature(l0, l1, depth), fix_depth(len).
+// feature covariance in register tiles), which provides run<RD>(E, n, len, H), init_feature(l0, l1, depth), fix_depth(len).
 template <int G>
 struct SmemCore {
   Ctx<G>& c;
   const KParams& p;
-  template <int RD, int MC>
-  __device__ __forceinline__ int run(const viekf_event& E, int n, int len, const HReg<RD, MC>& H) {
-    return update_core<G, RD, MC>(c, p, E, n, len, H);
+  template <int RD>
+  __device__ __forceinline__ int run(const viekf_event& E, int n, int len, const HReg& H) {
+    return update_core<G, RD>(c, p, E, n, len, H);
   }
   __device__ __forceinline__ bool init_feature(double l0, double l1, double depth) { return do_init_feature(c, p, l0, l1, depth); }
   __device__ __forceinline__ void fix_depth(int len) {
@@ -1056,9 +1060,16 @@ __device__ __forceinline__ int ev_update(Ctx<G>& c, const KParams& p, const viek
   }
   // ---- the three models the Monte-Carlo path lives on keep h, H and the residual in registers: every thread evaluates
   //      them from the same shared state, so no thread-0 section and no broadcast barrier ----
+  HReg H;
+#pragma unroll
+  for (int k = 0; k < 18; k++) H.h[k] = 0.0;
+#pragma unroll
+  for (int k = 0; k < 6; k++) H.col[k] = 0;
+  H.res[0] = H.res[1] = H.res[2] = 0.0;
+  H.m = 0;
+  H.hnan = false;
   if (type == VIEKF_FEAT && rd == 2) {  // h_feat, vi_ekf_meas.cpp:354-367
     const double* x = c.x;
-    HReg<2, 2> H;
     H.m = 2;
     H.col[0] = 16 + 3 * fi;
     H.col[1] = H.col[0] + 1;
@@ -1078,35 +1089,26 @@ __device__ __forceinline__ int ev_update(Ctx<G>& c, const KParams& p, const viek
 #pragma unroll
       for (int k = 0; k < 3; k++) fbs[k] = fb[0] * sk[k] + fb[1] * sk[3 + k] + fb[2] * sk[6 + k];
 #pragma unroll
-      for (int bb = 0; bb < 2; bb++) H.h[a * 2 + bb] = fbs[0] * Tm[bb] + fbs[1] * Tm[2 + bb] + fbs[2] * Tm[4 + bb];
+      for (int bb = 0; bb < 2; bb++) H.h[a * 6 + bb] = fbs[0] * Tm[bb] + fbs[1] * Tm[2 + bb] + fbs[2] * Tm[4 + bb];
     }
-    H.hnan = (H.h[0] != H.h[0]) || (H.h[1] != H.h[1]) || (H.h[2] != H.h[2]) || (H.h[3] != H.h[3]);
-    return core.template run<2, 2>(E, n, len, H);
-  }
-  if (type == VIEKF_ACC && p.use_drag && rd == 2) {  // h_acc drag model, vi_ekf_meas.cpp:281-296
+    H.hnan = (H.h[0] != H.h[0]) || (H.h[1] != H.h[1]) || (H.h[6] != H.h[6]) || (H.h[7] != H.h[7]);
+  } else if (type == VIEKF_ACC && p.use_drag && rd == 2) {  // h_acc drag model, vi_ekf_meas.cpp:281-296
     const double* x = c.x;
     const double mu = x[16];
-    HReg<2, 5> H;
     H.m = 5;
     H.col[0] = 3; H.col[1] = 4; H.col[2] = 9; H.col[3] = 10; H.col[4] = 15;
-#pragma unroll
-    for (int k = 0; k < 10; k++) H.h[k] = 0.0;
     H.h[0] = -mu; H.h[2] = 1.0; H.h[4] = -x[3];
-    H.h[5 + 1] = -mu; H.h[5 + 3] = 1.0; H.h[5 + 4] = -x[4];
+    H.h[6 + 1] = -mu; H.h[6 + 3] = 1.0; H.h[6 + 4] = -x[4];
     H.res[0] = zv[0] - (-mu * x[3] + x[10]);
     H.res[1] = zv[1] - (-mu * x[4] + x[11]);
     H.hnan = (mu != mu) || (x[3] != x[3]) || (x[4] != x[4]);
-    return core.template run<2, 5>(E, n, len, H);
-  }
-  if (type == VIEKF_ALT && rd == 1) {  // h_alt, vi_ekf_meas.cpp:308-315
-    HReg<1, 1> H;
+  } else if (type == VIEKF_ALT && rd == 1) {  // h_alt, vi_ekf_meas.cpp:308-315
     H.m = 1;
     H.col[0] = 2;
     H.h[0] = -1.0;
     H.res[0] = zv[0] - (-c.x[2]);
     H.hnan = false;
-    return core.template run<1, 1>(E, n, len, H);
-  }
+  } else {
   double* Hc = c.sm + SM_HC;   // [3][6]
   double* res = c.sm + SM_RES; // [4]
   int* cols = c.sc + SC_COUNT; // [6] + m + gate + nan
@@ -1213,9 +1215,12 @@ __device__ __forceinline__ int ev_update(Ctx<G>& c, const KParams& p, const viek
     if (hn) cols[8] = 1;
   }
   c.sync();
-  if (rd == 1) return update_generic<G, 1>(c, p, E, n, len, core);
-  if (rd == 2) return update_generic<G, 2>(c, p, E, n, len, core);
-  return update_generic<G, 3>(c, p, E, n, len, core);
+  load_h_from_smem(c, H);
+  }
+  // one call site per residual dimension
+  if (rd == 1) return core.template run<1>(E, n, len, H);
+  if (rd == 2) return core.template run<2>(E, n, len, H);
+  return core.template run<3>(E, n, len, H);
 }
 
 // ------------------------------------------------------------------------------------------------------------------

@@ -23,7 +23,7 @@ namespace vk {
 constexpr int PBS = 18;  // row stride of P_bb: even (16-byte rows for vector loads), 2-way conflicts at worst for row-per-lane access
 
 struct TLayout {
-  int x, Pbb, Pfb, Pfb2, lam, dx, Abd, AbT, T, Ac, Gb, Afd, Gd, Y, upd, small, ids, smap, total, TR;
+  int x, Pbb, Pfb, lam, dx, Abd, AbT, T, Ac, Gb, Afd, Gd, Y, upd, small, ids, smap, total, TR;
 };
 __host__ __device__ inline TLayout make_tlayout(int N) {
   TLayout L;
@@ -34,7 +34,6 @@ __host__ __device__ inline TLayout make_tlayout(int N) {
   L.x = o;     o += ev2(17 + 5 * N);
   L.Pbb = o;   o += 16 * PBS;           // full symmetric 16 x 16, row stride PBS
   L.Pfb = o;   o += ev2(3 * NP * 17);   // [feature row][17]: base columns 0..15, stride 17 (conflict-free row-per-lane access)
-  L.Pfb2 = o;  o += ev2(3 * NP * 17);   // second buffer: propagate and compaction write here, then the two are swapped
   L.lam = o;   o += ev2(nmaxp);
   L.dx = o;    o += ev2(nmaxp);
   L.Abd = o;   o += 256;
@@ -59,7 +58,7 @@ size_t tile_smem_bytes(int N) { return (size_t)make_tlayout(N).total * sizeof(do
 
 template <int TW>
 struct TCtx : Ctx<32 * (TW + 1)> {
-  double *Pbb, *Pfb, *Pfb2;
+  double *Pbb, *Pfb;
   int* smap;
   int ti, tj;   // tile coordinates in units of 2 features, ti >= tj
   bool tile;    // this thread owns a tile of the (capacity) grid
@@ -180,7 +179,7 @@ __device__ __forceinline__ void tile_propagate(TCtx<TW>& c, const KParams& p, co
     if (task < nfr) {
       const int fr = task, i = fr / 3;
       const double* Ad = c.Afd + fr * 19;
-#pragma unroll
+#pragma unroll 1
       for (int k = 3; k < 16; k++) {
         const double a = Ad[k];
         const double2* row = (const double2*)(c.Pbb + k * PBS);
@@ -203,7 +202,7 @@ __device__ __forceinline__ void tile_propagate(TCtx<TW>& c, const KParams& p, co
       for (int q = 0; q < 16; q++) Yr[q] = acc[q];
     } else {
       const int r = task - nfr;
-#pragma unroll
+#pragma unroll 1
       for (int k = 0; k < 16; k++) {
         const double a = c.Abd[r * 16 + k];
         const double2* row = (const double2*)(c.Pbb + k * PBS);
@@ -219,11 +218,13 @@ __device__ __forceinline__ void tile_propagate(TCtx<TW>& c, const KParams& p, co
     }
   }
   c.sync();
-  // ---- phase D: state boxplus; P'_ff tiles in registers; base warp: P'_bb in place (T holds A_bb P_bb), P'_fb into Pfb2 ----
+  // ---- phase D1: tiles: Z = A_ff,i P_ij + A_fb,i P_bf,j (last readers of the old P_fb); base warp: P'_bb in place (T holds
+  //      A_bb P_bb) and the state boxplus ----
+  const bool live_tile = c.tile && 2 * c.ti < len;
+  const int R = 6 * c.ti, C = 6 * c.tj;
   boxplus_inplace(c, c.dx, dt, len);
   if (c.tid == 0) *c.tcur = E.t;
-  if (c.tile && 2 * c.ti < len) {
-    const int R = 6 * c.ti, C = 6 * c.tj;
+  if (live_tile) {
     // Z = A_ff,i P_ij  (block rows), in place
 #pragma unroll
     for (int bi = 0; bi < 2; bi++) {
@@ -240,7 +241,7 @@ __device__ __forceinline__ void tile_propagate(TCtx<TW>& c, const KParams& p, co
       }
     }
     // Z += A_fb,i P_bf,j   (base columns VEL..MU: 3..15)
-#pragma unroll
+#pragma unroll 1
     for (int k = 3; k < 16; k++) {
       double ar[6], bc[6];
 #pragma unroll
@@ -252,6 +253,27 @@ __device__ __forceinline__ void tile_propagate(TCtx<TW>& c, const KParams& p, co
 #pragma unroll
         for (int cc = 0; cc < 6; cc++) PT(r, cc) = fma(ar[r], bc[cc], PT(r, cc));
     }
+  }
+  if (c.basew) {
+    // P'_bb = T A_bb^T + G_d Qu G_d^T + Qx: lower triangle, mirrored
+    for (int e = c.lane; e < 136; e += 32) {
+      int r = (int)((sqrtf(8.0f * (float)e + 1.0f) - 1.0f) * 0.5f);
+      while (((r + 1) * (r + 2) >> 1) <= e) r++;
+      while (((r * (r + 1)) >> 1) > e) r--;
+      const int cc = e - ((r * (r + 1)) >> 1);
+      double s = 0;
+#pragma unroll
+      for (int k = 0; k < 16; k++) s = fma(c.T[r * 16 + k], c.Abd[cc * 16 + k], s);
+#pragma unroll
+      for (int q = 0; q < 6; q++) s = fma(c.Gd[r * 6 + q] * p.Qu[q], c.Gd[cc * 6 + q], s);
+      if (r == cc) s += p.Qx[r];
+      c.Pbb[r * PBS + cc] = s;
+      c.Pbb[cc * PBS + r] = s;
+    }
+  }
+  c.sync();
+  // ---- phase D2: tiles: P'_ij = Z A_ff,j^T + Y_i A_fb,j^T + G_d,i Qu G_d,j^T; base warp: P'_fb = Y A_bb^T + ... in place ----
+  if (live_tile) {
     // O = Z A_ff,j^T  (block columns), in place
 #pragma unroll
     for (int bj = 0; bj < 2; bj++) {
@@ -268,7 +290,7 @@ __device__ __forceinline__ void tile_propagate(TCtx<TW>& c, const KParams& p, co
       }
     }
     // O += Y_i A_fb,j^T
-#pragma unroll
+#pragma unroll 1
     for (int k = 3; k < 16; k++) {
       double yr[6], ac[6];
 #pragma unroll
@@ -281,7 +303,7 @@ __device__ __forceinline__ void tile_propagate(TCtx<TW>& c, const KParams& p, co
         for (int cc = 0; cc < 6; cc++) PT(r, cc) = fma(yr[r], ac[cc], PT(r, cc));
     }
     // O += G_d,i Qu G_d,j^T
-#pragma unroll
+#pragma unroll 1
     for (int q = 0; q < 6; q++) {
       double gr[6], gc[6];
       const double qu = p.Qu[q];
@@ -305,21 +327,6 @@ __device__ __forceinline__ void tile_propagate(TCtx<TW>& c, const KParams& p, co
     tile_mirror(c, Pt);
   }
   if (c.basew) {
-    // P'_bb = T A_bb^T + G_d Qu G_d^T + Qx: lower triangle, mirrored
-    for (int e = c.lane; e < 136; e += 32) {
-      int r = (int)((sqrtf(8.0f * (float)e + 1.0f) - 1.0f) * 0.5f);
-      while (((r + 1) * (r + 2) >> 1) <= e) r++;
-      while (((r * (r + 1)) >> 1) > e) r--;
-      const int cc = e - ((r * (r + 1)) >> 1);
-      double s = 0;
-#pragma unroll
-      for (int k = 0; k < 16; k++) s = fma(c.T[r * 16 + k], c.Abd[cc * 16 + k], s);
-#pragma unroll
-      for (int q = 0; q < 6; q++) s = fma(c.Gd[r * 6 + q] * p.Qu[q], c.Gd[cc * 6 + q], s);
-      if (r == cc) s += p.Qx[r];
-      c.Pbb[r * PBS + cc] = s;
-      c.Pbb[cc * PBS + r] = s;
-    }
     // P'_fb = Y A_bb^T + G_d,f Qu G_d,b^T: lane = (row parity, base column)
     const int cc = c.lane & 15;
     double abt[16], gq[6];
@@ -342,15 +349,10 @@ __device__ __forceinline__ void tile_propagate(TCtx<TW>& c, const KParams& p, co
         s0 = fma(Gr[q], gq[q], s0);
         s1 = fma(Gr[q + 1], gq[q + 1], s1);
       }
-      c.Pfb2[fr * 17 + cc] = s0 + s1;
+      c.Pfb[fr * 17 + cc] = s0 + s1;
     }
   }
   c.sync();
-  {
-    double* t = c.Pfb;
-    c.Pfb = c.Pfb2;
-    c.Pfb2 = t;
-  }
   // ---- phase F: fix_depth ----
   tile_fix_depth(c, p, Pt, len);
 }
@@ -390,10 +392,11 @@ __device__ __forceinline__ double rank_delta(double2 wr, double2 kr, double w2r,
   return d;
 }
 
-template <int TW, int RD, int MC>
-__device__ __forceinline__ int tile_update_core(TCtx<TW>& c, const KParams& p, const viekf_event& E, int n, int len, const HReg<RD, MC>& H,
+template <int TW, int RD>
+__device__ __forceinline__ int tile_update_core(TCtx<TW>& c, const KParams& p, const viekf_event& E, int n, int len, const HReg& H,
                                                 double (&Pt)[36]) {
   constexpr int G = 32 * (TW + 1);
+  constexpr int MC = 6;
   int* cols = c.sc + SC_COUNT;
   const int lenp = (len + 1) & ~1;
   const int npad = 16 + 3 * lenp;
@@ -541,29 +544,33 @@ __device__ __forceinline__ int tile_update_core(TCtx<TW>& c, const KParams& p, c
   if (bad) atomicOr((unsigned*)&cols[8], 1u);
   c.sync();
   if (!cols[8]) {
-    boxplus_inplace(c, c.dx, 1.0, len);
+    boxplus_inplace(c, c.dx, 1.0, len, 32 * TW - 1);  // base part on the spare lane of the last tile warp: the base warp has the longer rank update
     if (c.tile && 2 * c.ti < len) {
       const int R = 16 + 6 * c.ti, C = 16 + 6 * c.tj;
-      double2 kc[6], hc[6];
-      double ac[6], k2c[6], h2c[6];
+      // three columns at a time: 72 tile registers + 3 column vectors + 1 row vector stay inside the register budget
 #pragma unroll
-      for (int cc = 0; cc < 6; cc++) {
-        kc[cc] = v.Kv[C + cc];
-        hc[cc] = v.Hv[C + cc];
-        ac[cc] = v.av[C + cc];
-        k2c[cc] = (RD == 3) ? v.K2[C + cc] : 0.0;
-        h2c[cc] = (RD == 3) ? v.H2[C + cc] : 0.0;
-      }
+      for (int ch = 0; ch < 2; ch++) {
+        double2 kc[3], hc[3];
+        double ac[3], k2c[3], h2c[3];
 #pragma unroll
-      for (int r = 0; r < 6; r++) {
-        const double2 wr = v.Wv[R + r], kr = v.Kv[R + r];
-        const double ar = v.av[R + r];
-        const double w2r = (RD == 3) ? v.W2[R + r] : 0.0, k2r = (RD == 3) ? v.K2[R + r] : 0.0;
+        for (int cc = 0; cc < 3; cc++) {
+          kc[cc] = v.Kv[C + 3 * ch + cc];
+          hc[cc] = v.Hv[C + 3 * ch + cc];
+          ac[cc] = v.av[C + 3 * ch + cc];
+          k2c[cc] = (RD == 3) ? v.K2[C + 3 * ch + cc] : 0.0;
+          h2c[cc] = (RD == 3) ? v.H2[C + 3 * ch + cc] : 0.0;
+        }
 #pragma unroll
-        for (int cc = 0; cc < 6; cc++) {
-          const double d = rank_delta<RD>(wr, kr, w2r, k2r, kc[cc], hc[cc], k2c[cc], h2c[cc]);
-          const double u = fma(-ar, ac[cc], 1.0);
-          PT(r, cc) = fma(d, u, PT(r, cc));
+        for (int r = 0; r < 6; r++) {
+          const double2 wr = v.Wv[R + r], kr = v.Kv[R + r];
+          const double ar = v.av[R + r];
+          const double w2r = (RD == 3) ? v.W2[R + r] : 0.0, k2r = (RD == 3) ? v.K2[R + r] : 0.0;
+#pragma unroll
+          for (int cc = 0; cc < 3; cc++) {
+            const double d = rank_delta<RD>(wr, kr, w2r, k2r, kc[cc], hc[cc], k2c[cc], h2c[cc]);
+            const double u = fma(-ar, ac[cc], 1.0);
+            PT(r, 3 * ch + cc) = fma(d, u, PT(r, 3 * ch + cc));
+          }
         }
       }
       tile_mirror(c, Pt);
@@ -667,8 +674,7 @@ __device__ __forceinline__ bool tile_init_feature(TCtx<TW>& c, const KParams& p,
 }
 
 // Order-preserving removal of features: new feature f <- old feature smap[f], f < newlen (clear_feature, vi_ekf_feat.cpp:50-73,
-// applied once for all removals).  Tiles go through the filter's packed P in global memory; x, ids and P_fb through registers
-// and the second P_fb buffer.  Precondition: smap[] published by a barrier.
+// applied once for all removals).  Tiles and P_fb go through the filter's packed P in global memory; x and ids through registers.  Precondition: smap[] published by a barrier.
 template <int TW>
 __device__ __forceinline__ void tile_compact(TCtx<TW>& c, const KParams& p, int len, int newlen, double (&Pt)[36]) {
   constexpr int G = 32 * (TW + 1);
@@ -682,21 +688,20 @@ __device__ __forceinline__ void tile_compact(TCtx<TW>& c, const KParams& p, int 
     for (int k = 0; k < 5; k++) xf[k] = c.x[17 + 5 * src + k];
     idv = c.ids[src];
   }
+  for (int e = c.tid; e < 3 * len * 16; e += G) {
+    const int fr = e >> 4, cc = e & 15;
+    gP[plo(16 + fr, cc)] = c.Pfb[fr * 17 + cc];
+  }
+  c.sync();
   const int newp = (newlen + 1) & ~1;
   for (int e = c.tid; e < 3 * newp * 16; e += G) {
     const int fr = e >> 4, cc = e & 15, f = fr / 3;
-    c.Pfb2[fr * 17 + cc] = (f < newlen) ? c.Pfb[(3 * c.smap[f] + (fr - 3 * f)) * 17 + cc] : 0.0;
+    c.Pfb[fr * 17 + cc] = (f < newlen) ? __ldcg(gP + plo(16 + 3 * c.smap[f] + (fr - 3 * f), cc)) : 0.0;
   }
-  c.sync();
   if (c.tid < newlen) {
 #pragma unroll
     for (int k = 0; k < 5; k++) c.x[17 + 5 * c.tid + k] = xf[k];
     c.ids[c.tid] = idv;
-  }
-  {
-    double* t = c.Pfb;
-    c.Pfb = c.Pfb2;
-    c.Pfb2 = t;
   }
   tile_load(c, gP, Pt, newlen, true);
   if (c.tid == 0) c.sc[SC_LEN] = newlen;
@@ -832,9 +837,9 @@ struct TileCore {
   TCtx<TW>& c;
   const KParams& p;
   double (&Pt)[36];
-  template <int RD, int MC>
-  __device__ __forceinline__ int run(const viekf_event& E, int n, int len, const HReg<RD, MC>& H) {
-    return tile_update_core<TW, RD, MC>(c, p, E, n, len, H, Pt);
+  template <int RD>
+  __device__ __forceinline__ int run(const viekf_event& E, int n, int len, const HReg& H) {
+    return tile_update_core<TW, RD>(c, p, E, n, len, H, Pt);
   }
   __device__ __forceinline__ bool init_feature(double l0, double l1, double depth) { return tile_init_feature(c, p, l0, l1, depth, Pt); }
   __device__ __forceinline__ void fix_depth(int len) { tile_fix_depth(c, p, Pt, len); }
@@ -844,7 +849,7 @@ struct TileCore {
 // the persistent tape executor, register-tile variant: one CTA of 32 (TW + 1) threads per filter at a time
 // ------------------------------------------------------------------------------------------------------------------
 template <int TW>
-__global__ void __launch_bounds__(32 * (TW + 1), (TW == 3 ? 3 : 1)) viekf_tile_kernel(const __grid_constant__ KParams p) {
+__global__ void __launch_bounds__(32 * (TW + 1), (TW == 3 ? 4 : 1)) viekf_tile_kernel(const __grid_constant__ KParams p) {
   extern __shared__ __align__(16) double smem[];
   constexpr int G = 32 * (TW + 1);
   const TLayout L = make_tlayout(p.N);
@@ -865,7 +870,7 @@ __global__ void __launch_bounds__(32 * (TW + 1), (TW == 3 ? 3 : 1)) viekf_tile_k
   double* base = smem;
   c.x = base + L.x; c.P = base + L.T; c.lam = base + L.lam; c.dx = base + L.dx; c.Abd = base + L.Abd; c.AbT = base + L.AbT; c.T = base + L.T;
   c.Ac = base + L.Ac; c.Gb = base + L.Gb; c.Afd = base + L.Afd; c.Gd = base + L.Gd; c.Y = base + L.Y; c.upd = base + L.upd;
-  c.Pbb = base + L.Pbb; c.Pfb = base + L.Pfb; c.Pfb2 = base + L.Pfb2;
+  c.Pbb = base + L.Pbb; c.Pfb = base + L.Pfb;
   c.sm = base + L.small;
   c.ids = (int*)(base + L.ids);
   c.rm = c.ids + p.N;
@@ -913,7 +918,7 @@ __global__ void __launch_bounds__(32 * (TW + 1), (TW == 3 ? 3 : 1)) viekf_tile_k
       const viekf_event& E = p.ev[e];
       const int kind = E.kind;
       c.zv = c.sm + SM_ZV + 8 * (int)((e - p.ev_first) & 1);
-      if (e + 1 < p.ev_first + p.ev_count && c.tid >= G - 32 && (c.tid & 31) < 8)
+      if (e + 1 < p.ev_first + p.ev_count && c.tid >= 32 && c.tid < 40)  // warp 1: idle while warp 0 / the base warp run the per-feature / base scalar work
         resolve_values(p, e + 1, b, ginst, c.tid & 31, c.sm + SM_ZV + 8 * (int)((e + 1 - p.ev_first) & 1));
       int result = VIEKF_MEAS_NONE;
       switch (kind) {
