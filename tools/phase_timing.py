@@ -1,0 +1,21 @@
+"""Phase timing of the tile executor (tuning helper).  Needs a build with NVFLAGS+=-DVIEKF_PHASE_TIMING:
+runs bench.py's workload, then prints the elapsed clocks per phase on the CTAs' critical path (see PH() in viekf_tile.cu)."""
+import ctypes, os, sys, io, contextlib, json
+ROOT = os.path.join(os.path.dirname(os.path.abspath(__file__)), "..")
+sys.path.insert(0, ROOT)
+import bench  # noqa: E402
+sys.argv = ["bench.py", "--no-cpu", "--filters", sys.argv[1] if len(sys.argv) > 1 else "32768", "--steps", "3", "--warmup", "3"]
+buf = io.StringIO()
+with contextlib.redirect_stdout(buf):
+    bench.main()
+d = json.loads([l for l in buf.getvalue().splitlines() if l.startswith("{")][-1])
+print("value %.4g ms/launch %s" % (d["value"], d["per_launch_ms"]))
+lib = ctypes.CDLL(bench.g.load_package().abi.lib_path())
+clk = (ctypes.c_ulonglong * 64)(); cnt = (ctypes.c_ulonglong * 64)()
+lib.viekf_debug_phase_clocks(clk, cnt, 0)
+names = {0: "load", 1: "PROP head+A+B", 2: "PROP C", 3: "PROP D1", 4: "PROP D2", 8: "UPD head+H", 9: "UPD PHt", 10: "UPD S,inv,K", 11: "UPD rank+boxplus",
+         15: "store", 16: "PROP F+end", 17: "UPD fix+end (or gated/new)", 18: "INIT", 19: "CLEAR", 20: "KEEP", 21: "STAT", 22: "KFRESET"}
+tot = sum(clk)
+for k in range(64):
+    if cnt[k]:
+        print(f"{names.get(k, k):28s} {100.0 * clk[k] / tot:5.1f}%  {clk[k] / cnt[k]:9.0f} clk/occurrence  x{cnt[k]}")

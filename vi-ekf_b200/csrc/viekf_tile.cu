@@ -56,6 +56,26 @@ __host__ __device__ inline TLayout make_tlayout(int N) {
 
 size_t tile_smem_bytes(int N) { return (size_t)make_tlayout(N).total * sizeof(double); }
 
+// Optional phase timing (build with -DVIEKF_PHASE_TIMING): thread 0 of every CTA adds the clocks between consecutive marks to
+// g_phase_clk[k]; since the marks sit right after barriers this is the elapsed time of each phase on the CTA's critical path.
+#ifdef VIEKF_PHASE_TIMING
+__device__ unsigned long long g_phase_clk[64];
+__device__ unsigned long long g_phase_cnt[64];
+#define PH_DECL long long ph_last;
+#define PH_INIT(c) (c).ph_last = clock64();
+#define PH(c, k)                                                     \
+  if (threadIdx.x == 0) {                                            \
+    const long long ph_now = clock64();                              \
+    atomicAdd(&g_phase_clk[k], (unsigned long long)(ph_now - (c).ph_last)); \
+    atomicAdd(&g_phase_cnt[k], 1ull);                                \
+    (c).ph_last = ph_now;                                            \
+  }
+#else
+#define PH_DECL
+#define PH_INIT(c)
+#define PH(c, k)
+#endif
+
 template <int TW>
 struct TCtx : Ctx<32 * (TW + 1)> {
   double *Pbb, *Pfb;
@@ -64,9 +84,11 @@ struct TCtx : Ctx<32 * (TW + 1)> {
   bool tile;    // this thread owns a tile of the (capacity) grid
   bool basew;   // this thread belongs to the base warp
   int lane;
+  PH_DECL
 };
 
 #define PT(r, c) Pt[(r) * 6 + (c)]
+
 
 template <int TW>
 __device__ __forceinline__ void tile_mirror(const TCtx<TW>& c, double (&Pt)[36]) {
@@ -169,6 +191,7 @@ __device__ __forceinline__ void tile_propagate(TCtx<TW>& c, const KParams& p, co
   double dt;
   int len;
   if (!prop_discretise(c, p, E, dt, len, 1)) return;
+  PH(c, 1)
   const int lenp = (len + 1) & ~1;
   const int nfr = 3 * lenp;
   // ---- phase C: one row of Y = A_fb P_bb + A_ff P_fb (3 lenp x 16) or of T = A_bb P_bb per thread ----
@@ -218,6 +241,7 @@ __device__ __forceinline__ void tile_propagate(TCtx<TW>& c, const KParams& p, co
     }
   }
   c.sync();
+  PH(c, 2)
   // ---- phase D1: tiles: Z = A_ff,i P_ij + A_fb,i P_bf,j (last readers of the old P_fb); base warp: P'_bb in place (T holds
   //      A_bb P_bb) and the state boxplus ----
   const bool live_tile = c.tile && 2 * c.ti < len;
@@ -272,6 +296,7 @@ __device__ __forceinline__ void tile_propagate(TCtx<TW>& c, const KParams& p, co
     }
   }
   c.sync();
+  PH(c, 3)
   // ---- phase D2: tiles: P'_ij = Z A_ff,j^T + Y_i A_fb,j^T + G_d,i Qu G_d,j^T; base warp: P'_fb = Y A_bb^T + ... in place ----
   if (live_tile) {
     // O = Z A_ff,j^T  (block columns), in place
@@ -353,6 +378,7 @@ __device__ __forceinline__ void tile_propagate(TCtx<TW>& c, const KParams& p, co
     }
   }
   c.sync();
+  PH(c, 4)
   // ---- phase F: fix_depth ----
   tile_fix_depth(c, p, Pt, len);
 }
@@ -401,6 +427,7 @@ __device__ __forceinline__ int tile_update_core(TCtx<TW>& c, const KParams& p, c
   const int lenp = (len + 1) & ~1;
   const int npad = 16 + 3 * lenp;
   TUpdVec v(c.upd, 16 + 3 * ((p.N + 1) & ~1));
+  PH(c, 8)
   const bool featcols = (H.m > 0) && (H.col[0] >= 16);  // every H touches either base columns or the columns of one feature
   // ---- P H^T ----
   if (!featcols) {
@@ -478,6 +505,7 @@ __device__ __forceinline__ int tile_update_core(TCtx<TW>& c, const KParams& p, c
   }
   if (c.tid == 0) cols[8] = H.hnan ? 1 : 0;
   c.sync();
+  PH(c, 9)
   // ---- S = H P H^T + R, S^-1, Mahalanobis gate: every thread evaluates the same registers ----
   double S[3][3], Si[3][3];
   {
@@ -543,6 +571,7 @@ __device__ __forceinline__ int tile_update_core(TCtx<TW>& c, const KParams& p, c
   }
   if (bad) atomicOr((unsigned*)&cols[8], 1u);
   c.sync();
+  PH(c, 10)
   if (!cols[8]) {
     boxplus_inplace(c, c.dx, 1.0, len, 32 * TW - 1);  // base part on the spare lane of the last tile warp: the base warp has the longer rank update
     if (c.tile && 2 * c.ti < len) {
@@ -618,6 +647,7 @@ __device__ __forceinline__ int tile_update_core(TCtx<TW>& c, const KParams& p, c
     c.sc[SC_NNAN] += 1;
   }
   c.sync();
+  PH(c, 11)
   tile_fix_depth(c, p, Pt, len);
   return VIEKF_MEAS_SUCCESS;
 }
@@ -880,6 +910,7 @@ __global__ void __launch_bounds__(32 * (TW + 1), (TW == 3 ? 4 : 1)) viekf_tile_k
   const int nmaxp = 16 + 6 * L.TR;
   for (int i = c.tid; i < nmaxp; i += G) c.lam[i] = (i < 16) ? p.lam[i] : p.lamf[(i - 16) % 3];
   double Pt[36];
+  PH_INIT(c)
 
   for (int64_t b = blockIdx.x; b < p.B; b += gridDim.x) {
     c.b = b;
@@ -913,6 +944,7 @@ __global__ void __launch_bounds__(32 * (TW + 1), (TW == 3 ? 4 : 1)) viekf_tile_k
     }
     if (p.ev_count > 0 && c.tid < 8) resolve_values(p, p.ev_first, b, ginst, c.tid, c.sm + SM_ZV);
     c.sync();
+    PH(c, 0)
     // ---- run the tape slice ----
     for (int64_t e = p.ev_first; e < p.ev_first + p.ev_count; e++) {
       const viekf_event& E = p.ev[e];
@@ -952,6 +984,7 @@ __global__ void __launch_bounds__(32 * (TW + 1), (TW == 3 ? 4 : 1)) viekf_tile_k
           break;
       }
       c.sync();
+      PH(c, 16 + kind)
       if (p.results && c.tid == 0 && b >= p.res_first && b < p.res_first + p.res_count)
         p.results[(b - p.res_first) * p.n_events + e] = (uint8_t)result;
     }
@@ -979,8 +1012,23 @@ __global__ void __launch_bounds__(32 * (TW + 1), (TW == 3 ? 4 : 1)) viekf_tile_k
       }
       tile_store(c, gP, Pt, len1);
     }
+    PH(c, 15)
   }
 }
+
+#ifdef VIEKF_PHASE_TIMING
+extern "C" int viekf_debug_phase_clocks(unsigned long long* clk, unsigned long long* cnt, int reset) {
+  cudaDeviceSynchronize();
+  cudaMemcpyFromSymbol(clk, g_phase_clk, sizeof(g_phase_clk));
+  cudaMemcpyFromSymbol(cnt, g_phase_cnt, sizeof(g_phase_cnt));
+  if (reset) {
+    static unsigned long long z[64];
+    cudaMemcpyToSymbol(g_phase_clk, z, sizeof(z));
+    cudaMemcpyToSymbol(g_phase_cnt, z, sizeof(z));
+  }
+  return 0;
+}
+#endif
 
 int tile_warps_for(int N) { return (N >= 7 && N <= 26) ? 3 : 0; }
 
