@@ -16,6 +16,7 @@
 // Padding: with `len` live features the tile grid covers lenp = len rounded up to even; every quantity of the padding
 // feature (A_d rows, G_d rows, Y rows, P_fb rows, update vectors, tile entries) is an exact zero, so no per-element guards
 // are needed inside the unrolled loops.
+#include <stdlib.h>
 #include "viekf_dev.cuh"
 
 namespace vk {
@@ -38,7 +39,7 @@ __host__ __device__ inline TLayout make_tlayout(int N) {
   L.dx = o;    o += ev2(nmaxp);
   L.Abd = o;   o += 256;
   L.AbT = o;   o += 256;
-  L.T = o;     o += 256;
+  L.T = o;     o += 16 * 17;             // A_bb P_bb, row stride 17 (conflict-free row-per-lane reads); also the packed P_bb copy
   L.Ac = o;    o += 144;
   L.Gb = o;    o += 54 + 2;
   L.Afd = o;   o += ev2(3 * NP * 19);
@@ -59,21 +60,27 @@ size_t tile_smem_bytes(int N) { return (size_t)make_tlayout(N).total * sizeof(do
 // Optional phase timing (build with -DVIEKF_PHASE_TIMING): thread 0 of every CTA adds the clocks between consecutive marks to
 // g_phase_clk[k]; since the marks sit right after barriers this is the elapsed time of each phase on the CTA's critical path.
 #ifdef VIEKF_PHASE_TIMING
-__device__ unsigned long long g_phase_clk[64];
-__device__ unsigned long long g_phase_cnt[64];
+__device__ unsigned long long g_phase_clk[4 * 64];
+__device__ unsigned long long g_phase_cnt[4 * 64];
 #define PH_DECL long long ph_last;
 #define PH_INIT(c) (c).ph_last = clock64();
-#define PH(c, k)                                                     \
-  if (threadIdx.x == 0) {                                            \
-    const long long ph_now = clock64();                              \
-    atomicAdd(&g_phase_clk[k], (unsigned long long)(ph_now - (c).ph_last)); \
-    atomicAdd(&g_phase_cnt[k], 1ull);                                \
-    (c).ph_last = ph_now;                                            \
+// slot k: work of the phase (mark before the barrier); slot k + 32: wait at the barrier (mark after it); one row per warp
+#define PH(c, k)                                                                                  \
+  if ((threadIdx.x & 31) == 0) {                                                                  \
+    const long long ph_now = clock64();                                                           \
+    atomicAdd(&g_phase_clk[64 * (threadIdx.x >> 5) + (k)], (unsigned long long)(ph_now - (c).ph_last)); \
+    atomicAdd(&g_phase_cnt[64 * (threadIdx.x >> 5) + (k)], 1ull);                                 \
+    (c).ph_last = ph_now;                                                                         \
   }
+#define PHS(c, k) \
+  PH(c, k)        \
+  (c).sync();     \
+  PH(c, (k) + 32)
 #else
 #define PH_DECL
 #define PH_INIT(c)
 #define PH(c, k)
+#define PHS(c, k) (c).sync();
 #endif
 
 template <int TW>
@@ -84,11 +91,31 @@ struct TCtx : Ctx<32 * (TW + 1)> {
   bool tile;    // this thread owns a tile of the (capacity) grid
   bool basew;   // this thread belongs to the base warp
   int lane;
+  // the next event's per-instance values are resolved (Philox noise, ~400 instructions on 8 lanes) by a warp that has slack
+  // in the current event: the base warp in propagate phase D2, warp 1 in the rank-update phase; otherwise by warp 1 up front
+  int64_t next_e;    // event to resolve, -1 = none
+  int64_t ginst;
+  double* zv_next;
+  bool resolved;
   PH_DECL
 };
 
+template <int TW>
+__device__ __forceinline__ void resolve_next(TCtx<TW>& c, const KParams& p, int first_tid) {
+  if (c.next_e >= 0 && c.tid >= first_tid && c.tid < first_tid + 8) resolve_values(p, c.next_e, c.b, c.ginst, c.tid - first_tid, c.zv_next);
+  c.resolved = true;
+}
+
 #define PT(r, c) Pt[(r) * 6 + (c)]
 
+
+// Base-warp threads own no tile: their Pt is all zeros for the whole launch.  Re-zeroing it at the end of a base-warp-only
+// section makes the 72 tile registers dead inside that section, so its loops get the full register budget (loads batched
+// ahead of the FMAs instead of one load-use round trip per FMA pair).
+__device__ __forceinline__ void tile_dead(double (&Pt)[36]) {
+#pragma unroll
+  for (int i = 0; i < 36; i++) Pt[i] = 0.0;
+}
 
 template <int TW>
 __device__ __forceinline__ void tile_mirror(const TCtx<TW>& c, double (&Pt)[36]) {
@@ -195,7 +222,8 @@ __device__ __forceinline__ void tile_propagate(TCtx<TW>& c, const KParams& p, co
   const int lenp = (len + 1) & ~1;
   const int nfr = 3 * lenp;
   // ---- phase C: one row of Y = A_fb P_bb + A_ff P_fb (3 lenp x 16) or of T = A_bb P_bb per thread ----
-  for (int task = c.tid; task < nfr + 16; task += G) {
+  // (Y rows on the tile warps, T rows on the base warp: no divergent warp)
+  for (int task = c.basew ? nfr + c.lane : c.tid; task < (c.basew ? nfr + 16 : nfr); task += 32 * TW) {
     double acc[16];
 #pragma unroll
     for (int q = 0; q < 16; q++) acc[q] = 0.0;
@@ -206,19 +234,24 @@ __device__ __forceinline__ void tile_propagate(TCtx<TW>& c, const KParams& p, co
       for (int k = 3; k < 16; k++) {
         const double a = Ad[k];
         const double2* row = (const double2*)(c.Pbb + k * PBS);
+        double2 v[8];  // the whole row first: eight loads in flight, then sixteen independent FMAs
+#pragma unroll
+        for (int q = 0; q < 8; q++) v[q] = row[q];
 #pragma unroll
         for (int q = 0; q < 8; q++) {
-          const double2 v = row[q];
-          acc[2 * q] = fma(a, v.x, acc[2 * q]);
-          acc[2 * q + 1] = fma(a, v.y, acc[2 * q + 1]);
+          acc[2 * q] = fma(a, v[q].x, acc[2 * q]);
+          acc[2 * q + 1] = fma(a, v[q].y, acc[2 * q + 1]);
         }
       }
 #pragma unroll
       for (int k = 0; k < 3; k++) {
         const double a = Ad[16 + k];
         const double* row = c.Pfb + (3 * i + k) * 17;
+        double v[16];
 #pragma unroll
-        for (int q = 0; q < 16; q++) acc[q] = fma(a, row[q], acc[q]);
+        for (int q = 0; q < 16; q++) v[q] = row[q];
+#pragma unroll
+        for (int q = 0; q < 16; q++) acc[q] = fma(a, v[q], acc[q]);
       }
       double* Yr = c.Y + fr * 17;
 #pragma unroll
@@ -229,19 +262,20 @@ __device__ __forceinline__ void tile_propagate(TCtx<TW>& c, const KParams& p, co
       for (int k = 0; k < 16; k++) {
         const double a = c.Abd[r * 16 + k];
         const double2* row = (const double2*)(c.Pbb + k * PBS);
+        double2 v[8];  // the whole row first: eight loads in flight, then sixteen independent FMAs
+#pragma unroll
+        for (int q = 0; q < 8; q++) v[q] = row[q];
 #pragma unroll
         for (int q = 0; q < 8; q++) {
-          const double2 v = row[q];
-          acc[2 * q] = fma(a, v.x, acc[2 * q]);
-          acc[2 * q + 1] = fma(a, v.y, acc[2 * q + 1]);
+          acc[2 * q] = fma(a, v[q].x, acc[2 * q]);
+          acc[2 * q + 1] = fma(a, v[q].y, acc[2 * q + 1]);
         }
       }
 #pragma unroll
-      for (int q = 0; q < 16; q++) c.T[r * 16 + q] = acc[q];
+      for (int q = 0; q < 16; q++) c.T[r * 17 + q] = acc[q];
     }
   }
-  c.sync();
-  PH(c, 2)
+  PHS(c, 2)
   // ---- phase D1: tiles: Z = A_ff,i P_ij + A_fb,i P_bf,j (last readers of the old P_fb); base warp: P'_bb in place (T holds
   //      A_bb P_bb) and the state boxplus ----
   const bool live_tile = c.tile && 2 * c.ti < len;
@@ -287,16 +321,16 @@ __device__ __forceinline__ void tile_propagate(TCtx<TW>& c, const KParams& p, co
       const int cc = e - ((r * (r + 1)) >> 1);
       double s = 0;
 #pragma unroll
-      for (int k = 0; k < 16; k++) s = fma(c.T[r * 16 + k], c.Abd[cc * 16 + k], s);
+      for (int k = 0; k < 16; k++) s = fma(c.T[r * 17 + k], c.AbT[k * 16 + cc], s);
 #pragma unroll
       for (int q = 0; q < 6; q++) s = fma(c.Gd[r * 6 + q] * p.Qu[q], c.Gd[cc * 6 + q], s);
       if (r == cc) s += p.Qx[r];
       c.Pbb[r * PBS + cc] = s;
       c.Pbb[cc * PBS + r] = s;
     }
+    tile_dead(Pt);
   }
-  c.sync();
-  PH(c, 3)
+  PHS(c, 3)
   // ---- phase D2: tiles: P'_ij = Z A_ff,j^T + Y_i A_fb,j^T + G_d,i Qu G_d,j^T; base warp: P'_fb = Y A_bb^T + ... in place ----
   if (live_tile) {
     // O = Z A_ff,j^T  (block columns), in place
@@ -352,33 +386,56 @@ __device__ __forceinline__ void tile_propagate(TCtx<TW>& c, const KParams& p, co
     tile_mirror(c, Pt);
   }
   if (c.basew) {
-    // P'_fb = Y A_bb^T + G_d,f Qu G_d,b^T: lane = (row parity, base column)
-    const int cc = c.lane & 15;
-    double abt[16], gq[6];
-#pragma unroll
-    for (int k = 0; k < 16; k++) abt[k] = c.AbT[k * 16 + cc];
-#pragma unroll
-    for (int q = 0; q < 6; q++) gq[q] = c.Gd[cc * 6 + q] * p.Qu[q];
-#pragma unroll 2
-    for (int fr = (c.lane >> 4); fr < nfr; fr += 2) {
+    // P'_fb = Y A_bb^T + G_d,f Qu G_d,b^T: one row per lane, 16 independent accumulators, operands as warp broadcasts.
+    // GqT[q][cc] = Qu[q] G_d(cc, q) goes to the T buffer (idle since D1).
+    double* GqT = c.T;
+    for (int e = c.lane; e < 96; e += 32) {
+      const int q = e >> 4, cc = e & 15;
+      GqT[e] = c.Gd[cc * 6 + q] * p.Qu[q];
+    }
+    __syncwarp();
+    for (int fr = c.lane; fr < nfr; fr += 32) {
       const double* Yr = c.Y + fr * 17;
       const double* Gr = c.Gd + (16 + fr) * 6;
-      double s0 = 0, s1 = 0;
+      double acc[16];
 #pragma unroll
-      for (int k = 0; k < 16; k += 2) {
-        s0 = fma(Yr[k], abt[k], s0);
-        s1 = fma(Yr[k + 1], abt[k + 1], s1);
-      }
+      for (int q = 0; q < 16; q++) acc[q] = 0.0;
+#pragma unroll 4
+      for (int k = 0; k < 16; k++) {
+        const double a = Yr[k];
+        const double2* row = (const double2*)(c.AbT + k * 16);
+        double2 v[8];  // the whole row first: eight loads in flight, then sixteen independent FMAs
 #pragma unroll
-      for (int q = 0; q < 6; q += 2) {
-        s0 = fma(Gr[q], gq[q], s0);
-        s1 = fma(Gr[q + 1], gq[q + 1], s1);
+        for (int q = 0; q < 8; q++) v[q] = row[q];
+#pragma unroll
+        for (int q = 0; q < 8; q++) {
+          acc[2 * q] = fma(a, v[q].x, acc[2 * q]);
+          acc[2 * q + 1] = fma(a, v[q].y, acc[2 * q + 1]);
+        }
       }
-      c.Pfb[fr * 17 + cc] = s0 + s1;
+#pragma unroll 2
+      for (int k = 0; k < 6; k++) {
+        const double a = Gr[k];
+        const double2* row = (const double2*)(GqT + k * 16);
+        double2 v[8];  // the whole row first: eight loads in flight, then sixteen independent FMAs
+#pragma unroll
+        for (int q = 0; q < 8; q++) v[q] = row[q];
+#pragma unroll
+        for (int q = 0; q < 8; q++) {
+          acc[2 * q] = fma(a, v[q].x, acc[2 * q]);
+          acc[2 * q + 1] = fma(a, v[q].y, acc[2 * q + 1]);
+        }
+      }
+      double* Pr = c.Pfb + fr * 17;
+#pragma unroll
+      for (int q = 0; q < 16; q++) Pr[q] = acc[q];
     }
+    resolve_next(c, p, 32 * TW);
+    tile_dead(Pt);
+  } else {
+    c.resolved = true;
   }
-  c.sync();
-  PH(c, 4)
+  PHS(c, 4)
   // ---- phase F: fix_depth ----
   tile_fix_depth(c, p, Pt, len);
 }
@@ -504,8 +561,7 @@ __device__ __forceinline__ int tile_update_core(TCtx<TW>& c, const KParams& p, c
     }
   }
   if (c.tid == 0) cols[8] = H.hnan ? 1 : 0;
-  c.sync();
-  PH(c, 9)
+  PHS(c, 9)
   // ---- S = H P H^T + R, S^-1, Mahalanobis gate: every thread evaluates the same registers ----
   double S[3][3], Si[3][3];
   {
@@ -570,8 +626,7 @@ __device__ __forceinline__ int tile_update_core(TCtx<TW>& c, const KParams& p, c
     c.dx[i] = p.use_partial ? li * d : d;
   }
   if (bad) atomicOr((unsigned*)&cols[8], 1u);
-  c.sync();
-  PH(c, 10)
+  PHS(c, 10)
   if (!cols[8]) {
     boxplus_inplace(c, c.dx, 1.0, len, 32 * TW - 1);  // base part on the spare lane of the last tile warp: the base warp has the longer rank update
     if (c.tile && 2 * c.ti < len) {
@@ -604,6 +659,7 @@ __device__ __forceinline__ int tile_update_core(TCtx<TW>& c, const KParams& p, c
       }
       tile_mirror(c, Pt);
     }
+    resolve_next(c, p, 32);
     if (c.basew) {
       // rows of [P_bb; P_fb]: one row per lane, three rows per pass; column vectors are warp broadcasts
       constexpr int NR = 3;
@@ -641,13 +697,13 @@ __device__ __forceinline__ int tile_update_core(TCtx<TW>& c, const KParams& p, c
             }
         }
       }
+      tile_dead(Pt);
     }
   } else if (c.tid == 0) {
     c.sc[SC_FLAGS] |= VIEKF_FLAG_NAN_GAIN;
     c.sc[SC_NNAN] += 1;
   }
-  c.sync();
-  PH(c, 11)
+  PHS(c, 11)
   tile_fix_depth(c, p, Pt, len);
   return VIEKF_MEAS_SUCCESS;
 }
@@ -915,6 +971,7 @@ __global__ void __launch_bounds__(32 * (TW + 1), (TW == 3 ? 4 : 1)) viekf_tile_k
   for (int64_t b = blockIdx.x; b < p.B; b += gridDim.x) {
     c.b = b;
     const int64_t ginst = p.inst_off + b;
+    c.ginst = ginst;
     FilterMeta& M = p.meta[b];
     double* gP = p.P + b * p.ps;
     // ---- load the filter: meta, ids, live part of x; P_bb / P_fb into shared memory, P_ff into the register tiles ----
@@ -943,15 +1000,16 @@ __global__ void __launch_bounds__(32 * (TW + 1), (TW == 3 ? 4 : 1)) viekf_tile_k
       tile_load(c, gP, Pt, len0, false);
     }
     if (p.ev_count > 0 && c.tid < 8) resolve_values(p, p.ev_first, b, ginst, c.tid, c.sm + SM_ZV);
-    c.sync();
-    PH(c, 0)
+    PHS(c, 0)
     // ---- run the tape slice ----
     for (int64_t e = p.ev_first; e < p.ev_first + p.ev_count; e++) {
       const viekf_event& E = p.ev[e];
       const int kind = E.kind;
       c.zv = c.sm + SM_ZV + 8 * (int)((e - p.ev_first) & 1);
-      if (e + 1 < p.ev_first + p.ev_count && c.tid >= 32 && c.tid < 40)  // warp 1: idle while warp 0 / the base warp run the per-feature / base scalar work
-        resolve_values(p, e + 1, b, ginst, c.tid & 31, c.sm + SM_ZV + 8 * (int)((e + 1 - p.ev_first) & 1));
+      c.next_e = (e + 1 < p.ev_first + p.ev_count) ? e + 1 : -1;
+      c.zv_next = c.sm + SM_ZV + 8 * (int)((e + 1 - p.ev_first) & 1);
+      c.resolved = false;
+      if (kind != VIEKF_EV_PROP && kind != VIEKF_EV_UPD) resolve_next(c, p, 32);
       int result = VIEKF_MEAS_NONE;
       switch (kind) {
         case VIEKF_EV_PROP:
@@ -983,8 +1041,8 @@ __global__ void __launch_bounds__(32 * (TW + 1), (TW == 3 ? 4 : 1)) viekf_tile_k
         default:
           break;
       }
-      c.sync();
-      PH(c, 16 + kind)
+      if (!c.resolved) resolve_next(c, p, 32);  // the handler returned before its deferred slot (uniform)
+      PHS(c, 16 + kind)
       if (p.results && c.tid == 0 && b >= p.res_first && b < p.res_first + p.res_count)
         p.results[(b - p.res_first) * p.n_events + e] = (uint8_t)result;
     }
@@ -1022,7 +1080,7 @@ extern "C" int viekf_debug_phase_clocks(unsigned long long* clk, unsigned long l
   cudaMemcpyFromSymbol(clk, g_phase_clk, sizeof(g_phase_clk));
   cudaMemcpyFromSymbol(cnt, g_phase_cnt, sizeof(g_phase_cnt));
   if (reset) {
-    static unsigned long long z[64];
+    static unsigned long long z[4 * 64];
     cudaMemcpyToSymbol(g_phase_clk, z, sizeof(z));
     cudaMemcpyToSymbol(g_phase_cnt, z, sizeof(z));
   }
@@ -1035,7 +1093,14 @@ int tile_warps_for(int N) { return (N >= 7 && N <= 26) ? 3 : 0; }
 cudaError_t launch_tile(const KParams& p, int sm_count, cudaStream_t stream) {
   constexpr int TW = 3;
   if (tile_warps_for(p.N) != TW) return cudaErrorInvalidValue;
-  const size_t smem = tile_smem_bytes(p.N);
+  size_t smem = tile_smem_bytes(p.N);
+  if (const char* s = getenv("VIEKF_TILE_MAXOCC")) {  // tuning aid: pad the shared-memory request so that at most k CTAs fit on an SM
+    const int k = atoi(s);
+    if (k >= 1 && k <= 8) {
+      const size_t pad = (size_t)(227 * 1024) / k - 2048;
+      if (pad > smem) smem = pad;
+    }
+  }
   cudaError_t e = cudaFuncSetAttribute(viekf_tile_kernel<TW>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   if (e != cudaSuccess) return e;
   e = cudaFuncSetAttribute(viekf_tile_kernel<TW>, cudaFuncAttributePreferredSharedMemoryCarveout, (int)cudaSharedmemCarveoutMaxShared);
