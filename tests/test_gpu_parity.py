@@ -251,6 +251,28 @@ def test_every_thread_group_mapping(pkg, oracle_mod, group, monkeypatch):
     _compare(bk, ref, tag=f"group={group}")
 
 
+@pytest.mark.parametrize("fpc", [1, 2, 4])
+def test_tile_executor_filters_per_cta(pkg, oracle_mod, fpc, monkeypatch):
+    """The register-tile executor with 1 / 2 / 4 filters per CTA in event lock-step (B = 6 leaves groups without a filter in
+    the last CTA) gives the same decisions and, bit for bit, the same numbers."""
+    monkeypatch.setenv("VIEKF_TILE_FPC", str(fpc))
+    cfg = _default_cfg()
+    NF, B = 9, 6
+    ev, idp, f, nb = tapes.consistent_tape(oracle_mod, cfg, NF, steps=48, seed=13)
+    ref = oracle_mod.run_batch(cfg, NF, ev, idp, count=B, nthreads=6, n_buckets=nb)
+    bk = pkg.BatchVIEKF(cfg, B=B, N=NF)
+    bk.stats_reset(nb)
+    res = bk.run_tape(ev, idp, results_first=0, results_count=B)
+    assert np.array_equal(res, ref["results"])
+    _compare(bk, ref, tag=f"fpc={fpc}")
+    _stats_close(bk.stats(nb), ref["stats"])
+    x, P = bk.get_state(), bk.get_covariance()
+    monkeypatch.setenv("VIEKF_TILE_FPC", "1")
+    b1 = pkg.BatchVIEKF(cfg, B=B, N=NF)
+    b1.run_tape(ev, idp)
+    assert np.array_equal(b1.get_state(), x) and np.array_equal(b1.get_covariance(), P)
+
+
 def test_edge_cases(pkg, oracle_mod):
     cfg = _default_cfg()
     bk = pkg.BatchVIEKF(cfg, B=2, N=2)

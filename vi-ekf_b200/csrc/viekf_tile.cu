@@ -24,7 +24,7 @@ namespace vk {
 constexpr int PBS = 18;  // row stride of P_bb: even (16-byte rows for vector loads), 2-way conflicts at worst for row-per-lane access
 
 struct TLayout {
-  int x, Pbb, Pfb, lam, dx, Abd, AbT, T, Ac, Gb, Afd, Gd, Y, upd, small, ids, smap, total, TR;
+  int x, Pbb, Pfb, lam, dx, Abd, AbT, T, Ac, Gb, Afd, Gd, Y, upd, small, ids, smap, evb, total, TR;
 };
 __host__ __device__ inline TLayout make_tlayout(int N) {
   TLayout L;
@@ -51,6 +51,7 @@ __host__ __device__ inline TLayout make_tlayout(int N) {
   L.small = o; o += 80;
   L.ids = o;   o += ev2(N + 12);
   L.smap = o;  o += ev2(NP / 2 + 2);
+  L.evb = o;   o += 64;                  // two staged viekf_event records (31 doubles each): the current and the next event
   L.total = ev2(o);
   return L;
 }
@@ -68,8 +69,8 @@ __device__ unsigned long long g_phase_cnt[4 * 64];
 #define PH(c, k)                                                                                  \
   if ((threadIdx.x & 31) == 0) {                                                                  \
     const long long ph_now = clock64();                                                           \
-    atomicAdd(&g_phase_clk[64 * (threadIdx.x >> 5) + (k)], (unsigned long long)(ph_now - (c).ph_last)); \
-    atomicAdd(&g_phase_cnt[64 * (threadIdx.x >> 5) + (k)], 1ull);                                 \
+    atomicAdd(&g_phase_clk[64 * ((threadIdx.x >> 5) & 3) + (k)], (unsigned long long)(ph_now - (c).ph_last)); \
+    atomicAdd(&g_phase_cnt[64 * ((threadIdx.x >> 5) & 3) + (k)], 1ull);                                 \
     (c).ph_last = ph_now;                                                                         \
   }
 #define PHS(c, k) \
@@ -209,6 +210,76 @@ __device__ __forceinline__ void tile_fix_depth(const TCtx<TW>& c, const KParams&
   }
 }
 
+// acc[0..W) += sum_{k<K} a[k * AS] * M[k * MS + 0..W), software-pipelined by hand: the 16 operands of row k+1 are loaded
+// before the 16 FMAs of row k are issued (ptxas otherwise pairs every load with its two consumers and exposes one
+// shared-memory round trip, ~29 clk, per FMA pair).  VEC: rows are 16-byte aligned (8 x LDS.128), else 16 x LDS.64.
+template <int W, bool VEC>
+__device__ __forceinline__ void load_row(double (&v)[W], const double* M) {
+  if (VEC) {
+    const double2* r = (const double2*)M;
+#pragma unroll
+    for (int q = 0; q < W / 2; q++) {
+      const double2 t = r[q];
+      v[2 * q] = t.x;
+      v[2 * q + 1] = t.y;
+    }
+  } else {
+#pragma unroll
+    for (int q = 0; q < W; q++) v[q] = M[q];
+  }
+}
+template <int W>
+__device__ __forceinline__ void fma_row(double (&acc)[W], double a, const double (&v)[W]) {
+#pragma unroll
+  for (int q = 0; q < W; q++) acc[q] = fma(a, v[q], acc[q]);
+}
+// W = 16 on threads with a free register file (base warp), W = 8 (two column halves) on threads that hold a tile
+template <int W, int K, int AS, int MS, bool VEC>
+__device__ __forceinline__ void rows(double (&acc)[W], const double* a, const double* M) {
+  double v[W], w[W];
+  load_row<W, VEC>(v, M);
+  double av = a[0], aw = 0.0;
+#pragma unroll 1
+  for (int k = 0; k + 2 <= K; k += 2) {
+    load_row<W, VEC>(w, M + (k + 1) * MS);
+    aw = a[(k + 1) * AS];
+    fma_row<W>(acc, av, v);
+    if (k + 2 < K) {
+      load_row<W, VEC>(v, M + (k + 2) * MS);
+      av = a[(k + 2) * AS];
+    }
+    fma_row<W>(acc, aw, w);
+  }
+  if (K & 1) fma_row<W>(acc, av, v);
+}
+
+// Base-warp loops live in out-of-line functions: the caller's 72 tile registers are dead there (tile_dead), so these get
+// their own register allocation and a latency-tolerant schedule (loads batched ahead of the FMAs) instead of the
+// pressure-minimising one the 128-register kernel body forces.
+//
+// P'_fb = Y A_bb^T + G_d,f Qu G_d,b^T: one row per lane, 16 independent accumulators, operands as warp broadcasts.
+// GqT[q][cc] = Qu[q] G_d(cc, q) goes to the T buffer (idle since D1).
+static __device__ __noinline__ void base_pfb(const double* Y, const double* AbT, const double* Gd, double* GqT, double* Pfb, const double* Qu, int nfr,
+                                             int lane) {
+  for (int e = lane; e < 96; e += 32) {
+    const int q = e >> 4, cc = e & 15;
+    GqT[e] = Gd[cc * 6 + q] * Qu[q];
+  }
+  __syncwarp();
+  for (int fr = lane; fr < nfr; fr += 32) {
+    const double* Yr = Y + fr * 17;
+    const double* Gr = Gd + (16 + fr) * 6;
+    double acc[16];
+#pragma unroll
+    for (int q = 0; q < 16; q++) acc[q] = 0.0;
+    rows<16, 16, 1, 16, true>(acc, Yr, AbT);
+    rows<16, 6, 1, 16, true>(acc, Gr, GqT);
+    double* Pr = Pfb + fr * 17;
+#pragma unroll
+    for (int q = 0; q < 16; q++) Pr[q] = acc[q];
+  }
+}
+
 // ------------------------------------------------------------------------------------------------------------------
 // PROP: propagate_state (vi_ekf.cpp:262-318) with the structured covariance product
 // ------------------------------------------------------------------------------------------------------------------
@@ -223,57 +294,31 @@ __device__ __forceinline__ void tile_propagate(TCtx<TW>& c, const KParams& p, co
   const int nfr = 3 * lenp;
   // ---- phase C: one row of Y = A_fb P_bb + A_ff P_fb (3 lenp x 16) or of T = A_bb P_bb per thread ----
   // (Y rows on the tile warps, T rows on the base warp: no divergent warp)
-  for (int task = c.basew ? nfr + c.lane : c.tid; task < (c.basew ? nfr + 16 : nfr); task += 32 * TW) {
+  if (!c.basew) {
+    for (int fr = c.tid; fr < nfr; fr += 32 * TW) {
+      const int i = fr / 3;
+      const double* Ad = c.Afd + fr * 19;
+      double* Yr = c.Y + fr * 17;
+#pragma unroll 1
+      for (int h = 0; h < 16; h += 8) {  // two column halves: 8 accumulators + two operand rows in flight next to the 72 tile registers
+        double acc[8];
+#pragma unroll
+        for (int q = 0; q < 8; q++) acc[q] = 0.0;
+        rows<8, 13, 1, PBS, true>(acc, Ad + 3, c.Pbb + 3 * PBS + h);
+        rows<8, 3, 1, 17, false>(acc, Ad + 16, c.Pfb + 3 * i * 17 + h);
+#pragma unroll
+        for (int q = 0; q < 8; q++) Yr[h + q] = acc[q];
+      }
+    }
+  } else if (c.lane < 16) {
+    const int r = c.lane;
     double acc[16];
 #pragma unroll
     for (int q = 0; q < 16; q++) acc[q] = 0.0;
-    if (task < nfr) {
-      const int fr = task, i = fr / 3;
-      const double* Ad = c.Afd + fr * 19;
-#pragma unroll 1
-      for (int k = 3; k < 16; k++) {
-        const double a = Ad[k];
-        const double2* row = (const double2*)(c.Pbb + k * PBS);
-        double2 v[8];  // the whole row first: eight loads in flight, then sixteen independent FMAs
+    rows<16, 16, 1, PBS, true>(acc, c.Abd + r * 16, c.Pbb);
 #pragma unroll
-        for (int q = 0; q < 8; q++) v[q] = row[q];
-#pragma unroll
-        for (int q = 0; q < 8; q++) {
-          acc[2 * q] = fma(a, v[q].x, acc[2 * q]);
-          acc[2 * q + 1] = fma(a, v[q].y, acc[2 * q + 1]);
-        }
-      }
-#pragma unroll
-      for (int k = 0; k < 3; k++) {
-        const double a = Ad[16 + k];
-        const double* row = c.Pfb + (3 * i + k) * 17;
-        double v[16];
-#pragma unroll
-        for (int q = 0; q < 16; q++) v[q] = row[q];
-#pragma unroll
-        for (int q = 0; q < 16; q++) acc[q] = fma(a, v[q], acc[q]);
-      }
-      double* Yr = c.Y + fr * 17;
-#pragma unroll
-      for (int q = 0; q < 16; q++) Yr[q] = acc[q];
-    } else {
-      const int r = task - nfr;
-#pragma unroll 1
-      for (int k = 0; k < 16; k++) {
-        const double a = c.Abd[r * 16 + k];
-        const double2* row = (const double2*)(c.Pbb + k * PBS);
-        double2 v[8];  // the whole row first: eight loads in flight, then sixteen independent FMAs
-#pragma unroll
-        for (int q = 0; q < 8; q++) v[q] = row[q];
-#pragma unroll
-        for (int q = 0; q < 8; q++) {
-          acc[2 * q] = fma(a, v[q].x, acc[2 * q]);
-          acc[2 * q + 1] = fma(a, v[q].y, acc[2 * q + 1]);
-        }
-      }
-#pragma unroll
-      for (int q = 0; q < 16; q++) c.T[r * 17 + q] = acc[q];
-    }
+    for (int q = 0; q < 16; q++) c.T[r * 17 + q] = acc[q];
+    tile_dead(Pt);
   }
   PHS(c, 2)
   // ---- phase D1: tiles: Z = A_ff,i P_ij + A_fb,i P_bf,j (last readers of the old P_fb); base warp: P'_bb in place (T holds
@@ -386,50 +431,7 @@ __device__ __forceinline__ void tile_propagate(TCtx<TW>& c, const KParams& p, co
     tile_mirror(c, Pt);
   }
   if (c.basew) {
-    // P'_fb = Y A_bb^T + G_d,f Qu G_d,b^T: one row per lane, 16 independent accumulators, operands as warp broadcasts.
-    // GqT[q][cc] = Qu[q] G_d(cc, q) goes to the T buffer (idle since D1).
-    double* GqT = c.T;
-    for (int e = c.lane; e < 96; e += 32) {
-      const int q = e >> 4, cc = e & 15;
-      GqT[e] = c.Gd[cc * 6 + q] * p.Qu[q];
-    }
-    __syncwarp();
-    for (int fr = c.lane; fr < nfr; fr += 32) {
-      const double* Yr = c.Y + fr * 17;
-      const double* Gr = c.Gd + (16 + fr) * 6;
-      double acc[16];
-#pragma unroll
-      for (int q = 0; q < 16; q++) acc[q] = 0.0;
-#pragma unroll 4
-      for (int k = 0; k < 16; k++) {
-        const double a = Yr[k];
-        const double2* row = (const double2*)(c.AbT + k * 16);
-        double2 v[8];  // the whole row first: eight loads in flight, then sixteen independent FMAs
-#pragma unroll
-        for (int q = 0; q < 8; q++) v[q] = row[q];
-#pragma unroll
-        for (int q = 0; q < 8; q++) {
-          acc[2 * q] = fma(a, v[q].x, acc[2 * q]);
-          acc[2 * q + 1] = fma(a, v[q].y, acc[2 * q + 1]);
-        }
-      }
-#pragma unroll 2
-      for (int k = 0; k < 6; k++) {
-        const double a = Gr[k];
-        const double2* row = (const double2*)(GqT + k * 16);
-        double2 v[8];  // the whole row first: eight loads in flight, then sixteen independent FMAs
-#pragma unroll
-        for (int q = 0; q < 8; q++) v[q] = row[q];
-#pragma unroll
-        for (int q = 0; q < 8; q++) {
-          acc[2 * q] = fma(a, v[q].x, acc[2 * q]);
-          acc[2 * q + 1] = fma(a, v[q].y, acc[2 * q + 1]);
-        }
-      }
-      double* Pr = c.Pfb + fr * 17;
-#pragma unroll
-      for (int q = 0; q < 16; q++) Pr[q] = acc[q];
-    }
+    base_pfb(c.Y, c.AbT, c.Gd, c.T, c.Pfb, p.Qu, nfr, c.lane);
     resolve_next(c, p, 32 * TW);
     tile_dead(Pt);
   } else {
@@ -473,6 +475,70 @@ __device__ __forceinline__ double rank_delta(double2 wr, double2 kr, double w2r,
     d = fma(-k2r, h2c, d);
   }
   return d;
+}
+
+// one column of the base-row rank update: the column's vectors (warp broadcasts) and the NR row entries of this lane
+template <int RD, int NR>
+struct BaseCol {
+  double2 kj, hj;
+  double aj, k2j, h2j, pv[NR];
+  __device__ __forceinline__ void load(const TUpdVec& v, double* const (&prow)[NR], int j) {
+    kj = v.Kv[j];
+    hj = v.Hv[j];
+    aj = v.av[j];
+    k2j = (RD == 3) ? v.K2[j] : 0.0;
+    h2j = (RD == 3) ? v.H2[j] : 0.0;
+#pragma unroll
+    for (int m = 0; m < NR; m++) pv[m] = prow[m][j];
+  }
+  __device__ __forceinline__ void apply(const double2 (&wr)[NR], const double2 (&kr)[NR], const double (&w2r)[NR], const double (&k2r)[NR],
+                                        const double (&ar)[NR], double* const (&prow)[NR], const int (&jmax)[NR], const int (&ii)[NR], double* Pbb,
+                                        int j) const {
+#pragma unroll
+    for (int m = 0; m < NR; m++)
+      if (j <= jmax[m]) {
+        const double d = rank_delta<RD>(wr[m], kr[m], w2r[m], k2r[m], kj, hj, k2j, h2j);
+        const double u = fma(-ar[m], aj, 1.0);
+        const double nv = fma(d, u, pv[m]);
+        prow[m][j] = nv;
+        if (ii[m] < 16) Pbb[j * PBS + ii[m]] = nv;
+      }
+  }
+};
+
+// rows of [P_bb; P_fb]: one row per lane, three rows per pass; column vectors are warp broadcasts (out of line: see base_pfb)
+template <int RD>
+static __device__ __noinline__ void base_rank(TUpdVec v, double* Pbb, double* Pfb, int npad, int lane) {
+  constexpr int NR = 3;
+  for (int ib = lane; ib < npad; ib += 32 * NR) {
+    double2 wr[NR], kr[NR];
+    double ar[NR], w2r[NR], k2r[NR];
+    double* prow[NR];
+    int jmax[NR], ii[NR];
+#pragma unroll
+    for (int m = 0; m < NR; m++) {
+      const int i = ib + 32 * m;
+      const bool valid = i < npad;
+      ii[m] = valid ? i : 0;
+      wr[m] = v.Wv[ii[m]];
+      kr[m] = v.Kv[ii[m]];
+      ar[m] = v.av[ii[m]];
+      w2r[m] = (RD == 3) ? v.W2[ii[m]] : 0.0;
+      k2r[m] = (RD == 3) ? v.K2[ii[m]] : 0.0;
+      prow[m] = (ii[m] < 16) ? Pbb + ii[m] * PBS : Pfb + (ii[m] - 16) * 17;
+      jmax[m] = valid ? (ii[m] < 16 ? ii[m] : 15) : -1;
+    }
+    // column j of the three rows, software-pipelined over pairs of columns (loads of column j+1 ahead of the FMAs of column j)
+    BaseCol<RD, NR> ca, cb;
+    ca.load(v, prow, 0);
+#pragma unroll 1
+    for (int j = 0; j < 16; j += 2) {
+      cb.load(v, prow, j + 1);
+      ca.apply(wr, kr, w2r, k2r, ar, prow, jmax, ii, Pbb, j);
+      if (j + 2 < 16) ca.load(v, prow, j + 2);
+      cb.apply(wr, kr, w2r, k2r, ar, prow, jmax, ii, Pbb, j + 1);
+    }
+  }
 }
 
 template <int TW, int RD>
@@ -661,42 +727,7 @@ __device__ __forceinline__ int tile_update_core(TCtx<TW>& c, const KParams& p, c
     }
     resolve_next(c, p, 32);
     if (c.basew) {
-      // rows of [P_bb; P_fb]: one row per lane, three rows per pass; column vectors are warp broadcasts
-      constexpr int NR = 3;
-      for (int ib = c.lane; ib < npad; ib += 32 * NR) {
-        double2 wr[NR], kr[NR];
-        double ar[NR], w2r[NR], k2r[NR];
-        double* prow[NR];
-        int jmax[NR], ii[NR];
-#pragma unroll
-        for (int m = 0; m < NR; m++) {
-          const int i = ib + 32 * m;
-          const bool valid = i < npad;
-          ii[m] = valid ? i : 0;
-          wr[m] = v.Wv[ii[m]];
-          kr[m] = v.Kv[ii[m]];
-          ar[m] = v.av[ii[m]];
-          w2r[m] = (RD == 3) ? v.W2[ii[m]] : 0.0;
-          k2r[m] = (RD == 3) ? v.K2[ii[m]] : 0.0;
-          prow[m] = (ii[m] < 16) ? c.Pbb + ii[m] * PBS : c.Pfb + (ii[m] - 16) * 17;
-          jmax[m] = valid ? (ii[m] < 16 ? ii[m] : 15) : -1;
-        }
-#pragma unroll 4
-        for (int j = 0; j < 16; j++) {
-          const double2 kj = v.Kv[j], hj = v.Hv[j];
-          const double aj = v.av[j];
-          const double k2j = (RD == 3) ? v.K2[j] : 0.0, h2j = (RD == 3) ? v.H2[j] : 0.0;
-#pragma unroll
-          for (int m = 0; m < NR; m++)
-            if (j <= jmax[m]) {
-              const double d = rank_delta<RD>(wr[m], kr[m], w2r[m], k2r[m], kj, hj, k2j, h2j);
-              const double u = fma(-ar[m], aj, 1.0);
-              const double nv = fma(d, u, prow[m][j]);
-              prow[m][j] = nv;
-              if (ii[m] < 16) c.Pbb[j * PBS + ii[m]] = nv;
-            }
-        }
-      }
+      base_rank<RD>(v, c.Pbb, c.Pfb, npad, c.lane);
       tile_dead(Pt);
     }
   } else if (c.tid == 0) {
@@ -932,20 +963,23 @@ struct TileCore {
 };
 
 // ------------------------------------------------------------------------------------------------------------------
-// the persistent tape executor, register-tile variant: one CTA of 32 (TW + 1) threads per filter at a time
+// the persistent tape executor, register-tile variant: a group of 32 (TW + 1) threads per filter, FPC groups per CTA.
+// The groups of a CTA synchronise among themselves with named barriers inside an event and all together at the end of
+// every event: the FPC filters stay within one event of each other, so the warps of an SM run the same few thousand
+// instructions at any time (the executor is instruction-fetch bound when its CTAs drift apart over the ~0.5 MB of code).
 // ------------------------------------------------------------------------------------------------------------------
-template <int TW>
-__global__ void __launch_bounds__(32 * (TW + 1), (TW == 3 ? 4 : 1)) viekf_tile_kernel(const __grid_constant__ KParams p) {
+template <int TW, int FPC>
+__global__ void __launch_bounds__(32 * (TW + 1) * FPC, (FPC == 1 ? 4 : (FPC == 2 ? 2 : 1))) viekf_tile_kernel(const __grid_constant__ KParams p) {
   extern __shared__ __align__(16) double smem[];
   constexpr int G = 32 * (TW + 1);
   const TLayout L = make_tlayout(p.N);
   TCtx<TW> c;
-  c.gi = 0;
-  c.tid = threadIdx.x;
-  c.lane = threadIdx.x & 31;
-  c.basew = (threadIdx.x >> 5) == TW;
+  c.gi = threadIdx.x / G;
+  c.tid = threadIdx.x % G;
+  c.lane = c.tid & 31;
+  c.basew = (c.tid >> 5) == TW;
   {
-    const int t = threadIdx.x;
+    const int t = c.tid;
     int ti = (int)((sqrtf(8.0f * (float)t + 1.0f) - 1.0f) * 0.5f);
     while (((ti + 1) * (ti + 2) >> 1) <= t) ti++;
     while (((ti * (ti + 1)) >> 1) > t) ti--;
@@ -953,7 +987,7 @@ __global__ void __launch_bounds__(32 * (TW + 1), (TW == 3 ? 4 : 1)) viekf_tile_k
     c.tj = t - ((ti * (ti + 1)) >> 1);
     c.tile = !c.basew && ti < L.TR;
   }
-  double* base = smem;
+  double* base = smem + (size_t)c.gi * L.total;
   c.x = base + L.x; c.P = base + L.T; c.lam = base + L.lam; c.dx = base + L.dx; c.Abd = base + L.Abd; c.AbT = base + L.AbT; c.T = base + L.T;
   c.Ac = base + L.Ac; c.Gb = base + L.Gb; c.Afd = base + L.Afd; c.Gd = base + L.Gd; c.Y = base + L.Y; c.upd = base + L.upd;
   c.Pbb = base + L.Pbb; c.Pfb = base + L.Pfb;
@@ -963,12 +997,17 @@ __global__ void __launch_bounds__(32 * (TW + 1), (TW == 3 ? 4 : 1)) viekf_tile_k
   c.sc = c.rm + p.N;
   c.smap = (int*)(base + L.smap);
   c.tcur = c.sm + SM_T;
+  double* evb = base + L.evb;
+  constexpr int EVW = (int)(sizeof(viekf_event) / sizeof(double));
+  static_assert(sizeof(viekf_event) % sizeof(double) == 0 && EVW <= 32, "viekf_event must fit one warp of doubles");
   const int nmaxp = 16 + 6 * L.TR;
   for (int i = c.tid; i < nmaxp; i += G) c.lam[i] = (i < 16) ? p.lam[i] : p.lamf[(i - 16) % 3];
   double Pt[36];
   PH_INIT(c)
 
-  for (int64_t b = blockIdx.x; b < p.B; b += gridDim.x) {
+  for (int64_t b0 = (int64_t)blockIdx.x * FPC; b0 < p.B; b0 += (int64_t)gridDim.x * FPC) {
+    const bool active = b0 + c.gi < p.B;  // a group without a filter still takes part in the CTA-wide event barriers
+    const int64_t b = active ? b0 + c.gi : 0;
     c.b = b;
     const int64_t ginst = p.inst_off + b;
     c.ginst = ginst;
@@ -1000,17 +1039,24 @@ __global__ void __launch_bounds__(32 * (TW + 1), (TW == 3 ? 4 : 1)) viekf_tile_k
       tile_load(c, gP, Pt, len0, false);
     }
     if (p.ev_count > 0 && c.tid < 8) resolve_values(p, p.ev_first, b, ginst, c.tid, c.sm + SM_ZV);
+    if (p.ev_count > 0 && c.tid >= 64 && c.tid < 64 + EVW) evb[c.tid - 64] = ((const double*)(p.ev + p.ev_first))[c.tid - 64];
     PHS(c, 0)
     // ---- run the tape slice ----
     for (int64_t e = p.ev_first; e < p.ev_first + p.ev_count; e++) {
-      const viekf_event& E = p.ev[e];
+      // the event record is read from shared memory; the next one is fetched now (one double per lane of warp 2) and
+      // staged just before the barrier that ends this event
+      const viekf_event& E = *(const viekf_event*)(evb + 32 * (int)((e - p.ev_first) & 1));
+      double ev_next = 0.0;
+      const bool stage = (e + 1 < p.ev_first + p.ev_count) && c.tid >= 64 && c.tid < 64 + EVW;
+      if (stage) ev_next = __ldg((const double*)(p.ev + e + 1) + (c.tid - 64));
       const int kind = E.kind;
       c.zv = c.sm + SM_ZV + 8 * (int)((e - p.ev_first) & 1);
       c.next_e = (e + 1 < p.ev_first + p.ev_count) ? e + 1 : -1;
       c.zv_next = c.sm + SM_ZV + 8 * (int)((e + 1 - p.ev_first) & 1);
       c.resolved = false;
-      if (kind != VIEKF_EV_PROP && kind != VIEKF_EV_UPD) resolve_next(c, p, 32);
       int result = VIEKF_MEAS_NONE;
+      if (active) {
+      if (kind != VIEKF_EV_PROP && kind != VIEKF_EV_UPD) resolve_next(c, p, 32);
       switch (kind) {
         case VIEKF_EV_PROP:
           tile_propagate(c, p, E, Pt);
@@ -1042,12 +1088,20 @@ __global__ void __launch_bounds__(32 * (TW + 1), (TW == 3 ? 4 : 1)) viekf_tile_k
           break;
       }
       if (!c.resolved) resolve_next(c, p, 32);  // the handler returned before its deferred slot (uniform)
-      PHS(c, 16 + kind)
-      if (p.results && c.tid == 0 && b >= p.res_first && b < p.res_first + p.res_count)
+      }
+      if (stage) evb[32 * (int)((e + 1 - p.ev_first) & 1) + (c.tid - 64)] = ev_next;
+      PH(c, 16 + kind)
+      if (FPC > 1)
+        __syncthreads();  // all filters of the CTA start the next event together
+      else
+        c.sync();
+      PH(c, 16 + kind + 32)
+      if (p.results && active && c.tid == 0 && b >= p.res_first && b < p.res_first + p.res_count)
         p.results[(b - p.res_first) * p.n_events + e] = (uint8_t)result;
     }
     // ---- store the filter ----
     c.sync();
+    if (!active) continue;
     const int len1 = c.sc[SC_LEN];
     if (c.tid == 0) {
       M.len = len1; M.next_id = c.sc[SC_NEXT]; M.started = c.sc[SC_STARTED]; M.flags = (uint32_t)c.sc[SC_FLAGS];
@@ -1090,10 +1144,10 @@ extern "C" int viekf_debug_phase_clocks(unsigned long long* clk, unsigned long l
 
 int tile_warps_for(int N) { return (N >= 7 && N <= 26) ? 3 : 0; }
 
-cudaError_t launch_tile(const KParams& p, int sm_count, cudaStream_t stream) {
-  constexpr int TW = 3;
-  if (tile_warps_for(p.N) != TW) return cudaErrorInvalidValue;
-  size_t smem = tile_smem_bytes(p.N);
+template <int TW, int FPC>
+static cudaError_t launch_tile_fpc(const KParams& p, int sm_count, cudaStream_t stream) {
+  constexpr int CTA = 32 * (TW + 1) * FPC;
+  size_t smem = tile_smem_bytes(p.N) * FPC;
   if (const char* s = getenv("VIEKF_TILE_MAXOCC")) {  // tuning aid: pad the shared-memory request so that at most k CTAs fit on an SM
     const int k = atoi(s);
     if (k >= 1 && k <= 8) {
@@ -1101,19 +1155,32 @@ cudaError_t launch_tile(const KParams& p, int sm_count, cudaStream_t stream) {
       if (pad > smem) smem = pad;
     }
   }
-  cudaError_t e = cudaFuncSetAttribute(viekf_tile_kernel<TW>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  cudaError_t e = cudaFuncSetAttribute(viekf_tile_kernel<TW, FPC>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   if (e != cudaSuccess) return e;
-  e = cudaFuncSetAttribute(viekf_tile_kernel<TW>, cudaFuncAttributePreferredSharedMemoryCarveout, (int)cudaSharedmemCarveoutMaxShared);
+  e = cudaFuncSetAttribute(viekf_tile_kernel<TW, FPC>, cudaFuncAttributePreferredSharedMemoryCarveout, (int)cudaSharedmemCarveoutMaxShared);
   if (e != cudaSuccess) return e;
   int occ = 0;
-  e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, viekf_tile_kernel<TW>, 32 * (TW + 1), smem);
+  e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, viekf_tile_kernel<TW, FPC>, CTA, smem);
   if (e != cudaSuccess) return e;
   if (occ < 1) return cudaErrorInvalidConfiguration;
   int64_t grid = (int64_t)sm_count * occ;  // persistent: a whole number of waves of the SM count
-  if (p.B < grid) grid = p.B;
+  const int64_t need = (p.B + FPC - 1) / FPC;
+  if (need < grid) grid = need;
   if (grid < 1) grid = 1;
-  viekf_tile_kernel<TW><<<(unsigned)grid, 32 * (TW + 1), smem, stream>>>(p);
+  viekf_tile_kernel<TW, FPC><<<(unsigned)grid, CTA, smem, stream>>>(p);
   return cudaGetLastError();
+}
+
+cudaError_t launch_tile(const KParams& p, int sm_count, cudaStream_t stream) {
+  constexpr int TW = 3;
+  if (tile_warps_for(p.N) != TW) return cudaErrorInvalidValue;
+  int fpc = (p.B < 4 * (int64_t)sm_count) ? 1 : 4;  // filters per CTA in event lock-step; small batches spread over the SMs first
+  if (const char* s = getenv("VIEKF_TILE_FPC")) fpc = atoi(s);
+  switch (fpc) {
+    case 1: return launch_tile_fpc<TW, 1>(p, sm_count, stream);
+    case 2: return launch_tile_fpc<TW, 2>(p, sm_count, stream);
+    default: return launch_tile_fpc<TW, 4>(p, sm_count, stream);
+  }
 }
 
 }  // namespace vk
