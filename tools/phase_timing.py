@@ -13,7 +13,7 @@ print("value %.4g ms/launch %s" % (d["value"], d["per_launch_ms"]))
 lib = ctypes.CDLL(bench.g.load_package().abi.lib_path())
 clk = (ctypes.c_ulonglong * 256)(); cnt = (ctypes.c_ulonglong * 256)()
 lib.viekf_debug_phase_clocks(clk, cnt, 0)
-names = {0: "load", 1: "PROP head+A+B", 2: "PROP C", 3: "PROP D1", 4: "PROP D2", 8: "UPD head+H", 9: "UPD PHt", 10: "UPD S,inv,K", 11: "UPD rank+boxplus",
+names = {0: "load", 1: "PROP head+A+B", 2: "PROP C", 3: "PROP D1", 4: "PROP D2", 8: "UPD head+H", 9: "UPD PHt", 10: "UPD S,inv,K", 11: "UPD resolve+rest", 12: "UPD  boxplus", 13: "UPD  tile rank", 14: "UPD  base rank",
          15: "store", 16: "PROP F", 17: "UPD fix (or gated/new)", 18: "INIT", 19: "CLEAR", 20: "KEEP", 21: "STAT", 22: "KFRESET"}
 tot = sum(clk[0:64])
 print("phase: per warp  work clk / wait-at-barrier clk per occurrence   (share of warp 0's time)")

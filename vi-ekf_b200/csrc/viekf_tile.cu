@@ -261,6 +261,11 @@ __device__ __forceinline__ void rows(double (&acc)[W], const double* a, const do
 // GqT[q][cc] = Qu[q] G_d(cc, q) goes to the T buffer (idle since D1).
 static __device__ __noinline__ void base_pfb(const double* Y, const double* AbT, const double* Gd, double* GqT, double* Pfb, const double* Qu, int nfr,
                                              int lane) {
+  __builtin_assume(__isShared(Y));
+  __builtin_assume(__isShared(AbT));
+  __builtin_assume(__isShared(Gd));
+  __builtin_assume(__isShared(GqT));
+  __builtin_assume(__isShared(Pfb));
   for (int e = lane; e < 96; e += 32) {
     const int q = e >> 4, cc = e & 15;
     GqT[e] = Gd[cc * 6 + q] * Qu[q];
@@ -325,7 +330,7 @@ __device__ __forceinline__ void tile_propagate(TCtx<TW>& c, const KParams& p, co
   //      A_bb P_bb) and the state boxplus ----
   const bool live_tile = c.tile && 2 * c.ti < len;
   const int R = 6 * c.ti, C = 6 * c.tj;
-  boxplus_inplace(c, c.dx, dt, len);
+  if (c.tid == G - 1 || c.tid < len) boxplus_inplace(c, c.dx, dt, len);  // only the warps with a share make the out-of-line call
   if (c.tid == 0) *c.tcur = E.t;
   if (live_tile) {
     // Z = A_ff,i P_ij  (block rows), in place
@@ -494,15 +499,20 @@ struct BaseCol {
   __device__ __forceinline__ void apply(const double2 (&wr)[NR], const double2 (&kr)[NR], const double (&w2r)[NR], const double (&k2r)[NR],
                                         const double (&ar)[NR], double* const (&prow)[NR], const int (&jmax)[NR], const int (&ii)[NR], double* Pbb,
                                         int j) const {
+    // all NR elements first (independent FMA chains interleave), then the guarded stores: no divergent region per element
+    double nv[NR];
 #pragma unroll
-    for (int m = 0; m < NR; m++)
-      if (j <= jmax[m]) {
-        const double d = rank_delta<RD>(wr[m], kr[m], w2r[m], k2r[m], kj, hj, k2j, h2j);
-        const double u = fma(-ar[m], aj, 1.0);
-        const double nv = fma(d, u, pv[m]);
-        prow[m][j] = nv;
-        if (ii[m] < 16) Pbb[j * PBS + ii[m]] = nv;
-      }
+    for (int m = 0; m < NR; m++) {
+      const double d = rank_delta<RD>(wr[m], kr[m], w2r[m], k2r[m], kj, hj, k2j, h2j);
+      const double u = fma(-ar[m], aj, 1.0);
+      nv[m] = fma(d, u, pv[m]);
+    }
+#pragma unroll
+    for (int m = 0; m < NR; m++) {
+      const bool ok = j <= jmax[m];
+      if (ok) prow[m][j] = nv[m];
+      if (ok && ii[m] < 16) Pbb[j * PBS + ii[m]] = nv[m];
+    }
   }
 };
 
@@ -510,6 +520,16 @@ struct BaseCol {
 template <int RD>
 static __device__ __noinline__ void base_rank(TUpdVec v, double* Pbb, double* Pfb, int npad, int lane) {
   constexpr int NR = 3;
+  // every pointer is into shared memory: lets the compiler emit LDS / STS instead of generic loads and stores
+  __builtin_assume(__isShared(Pbb));
+  __builtin_assume(__isShared(Pfb));
+  __builtin_assume(__isShared(v.Kv));
+  __builtin_assume(__isShared(v.Hv));
+  __builtin_assume(__isShared(v.Wv));
+  __builtin_assume(__isShared(v.K2));
+  __builtin_assume(__isShared(v.H2));
+  __builtin_assume(__isShared(v.W2));
+  __builtin_assume(__isShared(v.av));
   for (int ib = lane; ib < npad; ib += 32 * NR) {
     double2 wr[NR], kr[NR];
     double ar[NR], w2r[NR], k2r[NR];
@@ -694,7 +714,10 @@ __device__ __forceinline__ int tile_update_core(TCtx<TW>& c, const KParams& p, c
   if (bad) atomicOr((unsigned*)&cols[8], 1u);
   PHS(c, 10)
   if (!cols[8]) {
-    boxplus_inplace(c, c.dx, 1.0, len, 32 * TW - 1);  // base part on the spare lane of the last tile warp: the base warp has the longer rank update
+    // base part on the spare lane of the last tile warp (the base warp has the longer rank update); warps without a share of the
+    // boxplus skip the out-of-line call altogether
+    if (c.tid == 32 * TW - 1 || c.tid < len) boxplus_inplace(c, c.dx, 1.0, len, 32 * TW - 1);
+    PH(c, 12)
     if (c.tile && 2 * c.ti < len) {
       const int R = 16 + 6 * c.ti, C = 16 + 6 * c.tj;
       // three columns at a time: 72 tile registers + 3 column vectors + 1 row vector stay inside the register budget
@@ -725,9 +748,11 @@ __device__ __forceinline__ int tile_update_core(TCtx<TW>& c, const KParams& p, c
       }
       tile_mirror(c, Pt);
     }
+    PH(c, 13)
     resolve_next(c, p, 32);
     if (c.basew) {
       base_rank<RD>(v, c.Pbb, c.Pfb, npad, c.lane);
+      PH(c, 14)
       tile_dead(Pt);
     }
   } else if (c.tid == 0) {
@@ -1179,6 +1204,7 @@ cudaError_t launch_tile(const KParams& p, int sm_count, cudaStream_t stream) {
   switch (fpc) {
     case 1: return launch_tile_fpc<TW, 1>(p, sm_count, stream);
     case 2: return launch_tile_fpc<TW, 2>(p, sm_count, stream);
+    case 3: return launch_tile_fpc<TW, 3>(p, sm_count, stream);
     default: return launch_tile_fpc<TW, 4>(p, sm_count, stream);
   }
 }
