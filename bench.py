@@ -283,12 +283,12 @@ def emit(args, pkg, world, K, W, B, ev, idp, info, slices, cfg, ms_total, ms_e2e
     hbm_peak = float(peaks.get("hbm_gbs", 6650.0))
     hbm_bytes = B * pkg.sim.hbm_bytes_per_launch(N_FEAT)
     traffic = None
-    try:
-        traffic = json.load(open(os.path.join(ROOT, "profiles", "traffic.json"))).get("dram_bytes_per_launch")
+    try:  # dram__bytes_read + dram__bytes_write of one launch from the ncu --set full capture, recorded per filter
+        traffic = json.load(open(os.path.join(ROOT, "profiles", "traffic.json"))).get("dram_bytes_per_filter_per_launch") * B
     except Exception:
         pass
     roofline = {
-        "bound": "fp64", "kernel": "viekf_tape_kernel<256>", "achieved": achieved_tf, "peak": fp64_peak, "unit": "TFLOP/s",
+        "bound": "fp64", "kernel": "viekf_tile_kernel<3,3> (register-tile tape executor, 3 filters per CTA)", "achieved": achieved_tf, "peak": fp64_peak, "unit": "TFLOP/s",
         "frac": achieved_tf / fp64_peak if fp64_peak > 0 else None, "traffic": traffic,
         "peak_source": "viekf_fp64_peak_probe (DFMA microbenchmark run by this bench; MEASURED_PEAKS.json has no FP64 figure)",
         "flops_per_launch": flops_per_launch, "avg_launch_ms": avg_launch_s * 1e3, "gated_update_fraction": gated_frac,

@@ -1199,7 +1199,9 @@ static cudaError_t launch_tile_fpc(const KParams& p, int sm_count, cudaStream_t 
 cudaError_t launch_tile(const KParams& p, int sm_count, cudaStream_t stream) {
   constexpr int TW = 3;
   if (tile_warps_for(p.N) != TW) return cudaErrorInvalidValue;
-  int fpc = (p.B < 4 * (int64_t)sm_count) ? 1 : 4;  // filters per CTA in event lock-step; small batches spread over the SMs first
+  // filters per CTA in event lock-step: 3 (384 threads, 168 registers each: the 72-register tile plus a schedule with loads
+  // in flight; 4 x 128 registers spills on the hot path); small batches spread over the SMs first
+  int fpc = (p.B < 3 * (int64_t)sm_count) ? 1 : 3;
   if (const char* s = getenv("VIEKF_TILE_FPC")) fpc = atoi(s);
   switch (fpc) {
     case 1: return launch_tile_fpc<TW, 1>(p, sm_count, stream);
