@@ -24,7 +24,7 @@ namespace vk {
 constexpr int PBS = 18;  // row stride of P_bb: even (16-byte rows for vector loads), 2-way conflicts at worst for row-per-lane access
 
 struct TLayout {
-  int x, Pbb, Pfb, lam, dx, Abd, AbT, T, Ac, Gb, Afd, Gd, Y, upd, small, ids, smap, evb, total, TR;
+  int x, Pbb, Pfb, lam, dx, Abd, AbT, T, Ac, Gb, Afd, Gd, Y, upd, small, ids, smap, evb, fixk, fixv, total, TR;
 };
 __host__ __device__ inline TLayout make_tlayout(int N) {
   TLayout L;
@@ -52,6 +52,8 @@ __host__ __device__ inline TLayout make_tlayout(int N) {
   L.ids = o;   o += ev2(N + 12);
   L.smap = o;  o += ev2(NP / 2 + 2);
   L.evb = o;   o += 64;                  // two staged viekf_event records (31 doubles each): the current and the next event
+  L.fixk = o;  o += ev2(NP / 2 + 1);     // pending fix_depth covariance corrections per feature: kind (int32) ...
+  L.fixv = o;  o += NP;                  // ... and value
   L.total = ev2(o);
   return L;
 }
@@ -86,8 +88,8 @@ __device__ unsigned long long g_phase_cnt[4 * 64];
 
 template <int TW>
 struct TCtx : Ctx<32 * (TW + 1)> {
-  double *Pbb, *Pfb;
-  int* smap;
+  double *Pbb, *Pfb, *fixv;
+  int *smap, *fixk;
   int ti, tj;   // tile coordinates in units of 2 features, ti >= tj
   bool tile;    // this thread owns a tile of the (capacity) grid
   bool basew;   // this thread belongs to the base warp
@@ -172,40 +174,54 @@ __device__ __forceinline__ void tile_store(const TCtx<TW>& c, double* gP, const 
     }
 }
 
-// fix_depth (vi_ekf_helper.cpp:128-156): the thread that owns the diagonal tile handles its two features
+// fix_depth (vi_ekf_helper.cpp:128-156), split so that it needs no barrier of its own: the thread that just box-plussed
+// feature i checks its inverse depth, resets it and records the covariance correction (P_rr += err^2, or P_rr = P0_feat);
+// the owner of the diagonal tile applies the recorded correction after the barrier that ends the event, before anything
+// reads P again.
 template <int TW>
-__device__ __forceinline__ void tile_fix_depth(const TCtx<TW>& c, const KParams& p, double (&Pt)[36], int len) {
+__device__ __forceinline__ void tile_fix_x(const TCtx<TW>& c, const KParams& p, int i) {
+  double* rho = c.x + 17 + 5 * i + 4;
+  const double reset = 1.0 / (2.0 * p.min_depth);
+  double r = *rho;
+  uint32_t fl = 0;
+  int nfix = 0;
+  if (r != r) {
+    r = reset;
+    fl |= VIEKF_FLAG_DEPTH_NAN_FIXED;
+    nfix++;
+  }
+  if (r < 0.0) {
+    const double err = reset - r;
+    c.fixv[i] = err * err;
+    c.fixk[i] = 1;
+    r = reset;
+    fl |= VIEKF_FLAG_DEPTH_NEG_FIXED;
+    nfix++;
+  } else if (r > 1e2) {
+    c.fixk[i] = 2;
+    r = reset;
+    fl |= VIEKF_FLAG_DEPTH_BIG_FIXED;
+    nfix++;
+  }
+  if (nfix) {
+    *rho = r;
+    atomicOr((unsigned*)&c.sc[SC_FLAGS], fl);
+    atomicAdd(&c.sc[SC_NFIX], nfix);
+  }
+}
+template <int TW>
+__device__ __forceinline__ void tile_apply_fix(const TCtx<TW>& c, const KParams& p, double (&Pt)[36]) {
   if (!(c.tile && c.ti == c.tj)) return;
 #pragma unroll
   for (int bi = 0; bi < 2; bi++) {
     const int i = 2 * c.ti + bi;
-    if (i >= len) continue;
-    double* rho = c.x + 17 + 5 * i + 4;
-    const double reset = 1.0 / (2.0 * p.min_depth);
-    double r = *rho;
-    uint32_t fl = 0;
-    int nfix = 0;
-    if (r != r) {
-      r = reset;
-      fl |= VIEKF_FLAG_DEPTH_NAN_FIXED;
-      nfix++;
-    }
-    if (r < 0.0) {
-      const double err = reset - r;
-      PT(3 * bi + 2, 3 * bi + 2) += err * err;
-      r = reset;
-      fl |= VIEKF_FLAG_DEPTH_NEG_FIXED;
-      nfix++;
-    } else if (r > 1e2) {
-      PT(3 * bi + 2, 3 * bi + 2) = p.P0f[2];
-      r = reset;
-      fl |= VIEKF_FLAG_DEPTH_BIG_FIXED;
-      nfix++;
-    }
-    if (nfix) {
-      *rho = r;
-      atomicOr((unsigned*)&c.sc[SC_FLAGS], fl);
-      atomicAdd(&c.sc[SC_NFIX], nfix);
+    const int k = c.fixk[i];
+    if (k) {
+      if (k == 1)
+        PT(3 * bi + 2, 3 * bi + 2) += c.fixv[i];
+      else
+        PT(3 * bi + 2, 3 * bi + 2) = p.P0f[2];
+      c.fixk[i] = 0;
     }
   }
 }
@@ -331,6 +347,7 @@ __device__ __forceinline__ void tile_propagate(TCtx<TW>& c, const KParams& p, co
   const bool live_tile = c.tile && 2 * c.ti < len;
   const int R = 6 * c.ti, C = 6 * c.tj;
   if (c.tid == G - 1 || c.tid < len) boxplus_inplace(c, c.dx, dt, len);  // only the warps with a share make the out-of-line call
+  if (c.tid < len) tile_fix_x(c, p, c.tid);  // phase F of the other executor, by the thread that owns the feature's state
   if (c.tid == 0) *c.tcur = E.t;
   if (live_tile) {
     // Z = A_ff,i P_ij  (block rows), in place
@@ -442,9 +459,8 @@ __device__ __forceinline__ void tile_propagate(TCtx<TW>& c, const KParams& p, co
   } else {
     c.resolved = true;
   }
-  PHS(c, 4)
-  // ---- phase F: fix_depth ----
-  tile_fix_depth(c, p, Pt, len);
+  PH(c, 4)
+  // no barrier here: the one that ends the event publishes P'_fb, the resolved values and the pending depth corrections
 }
 
 // ------------------------------------------------------------------------------------------------------------------
@@ -595,7 +611,7 @@ __device__ __forceinline__ int tile_update_core(TCtx<TW>& c, const KParams& p, c
 #pragma unroll
       for (int kk = 0; kk < 3; kk++) he[a][kk] = 0.0;
 #pragma unroll
-    for (int k = 0; k < MC; k++)
+    for (int k = 0; k < 2; k++)  // feature-column models have at most two live columns (FEAT, QZETA: 2; DEPTH, INV_DEPTH: 1)
       if (k < H.m) {
         const int lk = H.col[k] - 16 - 3 * fi;
 #pragma unroll
@@ -759,8 +775,8 @@ __device__ __forceinline__ int tile_update_core(TCtx<TW>& c, const KParams& p, c
     c.sc[SC_FLAGS] |= VIEKF_FLAG_NAN_GAIN;
     c.sc[SC_NNAN] += 1;
   }
-  PHS(c, 11)
-  tile_fix_depth(c, p, Pt, len);
+  if (c.tid < len) tile_fix_x(c, p, c.tid);
+  PH(c, 11)
   return VIEKF_MEAS_SUCCESS;
 }
 
@@ -984,7 +1000,9 @@ struct TileCore {
     return tile_update_core<TW, RD>(c, p, E, n, len, H, Pt);
   }
   __device__ __forceinline__ bool init_feature(double l0, double l1, double depth) { return tile_init_feature(c, p, l0, l1, depth, Pt); }
-  __device__ __forceinline__ void fix_depth(int len) { tile_fix_depth(c, p, Pt, len); }
+  __device__ __forceinline__ void fix_depth(int len) {
+    if (c.tid < len) tile_fix_x(c, p, c.tid);
+  }
 };
 
 // ------------------------------------------------------------------------------------------------------------------
@@ -1021,12 +1039,15 @@ __global__ void __launch_bounds__(32 * (TW + 1) * FPC, (FPC == 1 ? 4 : (FPC == 2
   c.rm = c.ids + p.N;
   c.sc = c.rm + p.N;
   c.smap = (int*)(base + L.smap);
+  c.fixk = (int*)(base + L.fixk);
+  c.fixv = base + L.fixv;
   c.tcur = c.sm + SM_T;
   double* evb = base + L.evb;
   constexpr int EVW = (int)(sizeof(viekf_event) / sizeof(double));
   static_assert(sizeof(viekf_event) % sizeof(double) == 0 && EVW <= 32, "viekf_event must fit one warp of doubles");
   const int nmaxp = 16 + 6 * L.TR;
   for (int i = c.tid; i < nmaxp; i += G) c.lam[i] = (i < 16) ? p.lam[i] : p.lamf[(i - 16) % 3];
+  for (int i = c.tid; i < 2 * L.TR; i += G) c.fixk[i] = 0;
   double Pt[36];
   PH_INIT(c)
 
@@ -1071,6 +1092,7 @@ __global__ void __launch_bounds__(32 * (TW + 1) * FPC, (FPC == 1 ? 4 : (FPC == 2
       // the event record is read from shared memory; the next one is fetched now (one double per lane of warp 2) and
       // staged just before the barrier that ends this event
       const viekf_event& E = *(const viekf_event*)(evb + 32 * (int)((e - p.ev_first) & 1));
+      tile_apply_fix(c, p, Pt);  // depth corrections recorded by the previous event
       double ev_next = 0.0;
       const bool stage = (e + 1 < p.ev_first + p.ev_count) && c.tid >= 64 && c.tid < 64 + EVW;
       if (stage) ev_next = __ldg((const double*)(p.ev + e + 1) + (c.tid - 64));
@@ -1127,6 +1149,7 @@ __global__ void __launch_bounds__(32 * (TW + 1) * FPC, (FPC == 1 ? 4 : (FPC == 2
     // ---- store the filter ----
     c.sync();
     if (!active) continue;
+    tile_apply_fix(c, p, Pt);
     const int len1 = c.sc[SC_LEN];
     if (c.tid == 0) {
       M.len = len1; M.next_id = c.sc[SC_NEXT]; M.started = c.sc[SC_STARTED]; M.flags = (uint32_t)c.sc[SC_FLAGS];
