@@ -498,40 +498,6 @@ __device__ __forceinline__ double rank_delta(double2 wr, double2 kr, double w2r,
   return d;
 }
 
-// one column of the base-row rank update: the column's vectors (warp broadcasts) and the NR row entries of this lane
-template <int RD, int NR>
-struct BaseCol {
-  double2 kj, hj;
-  double aj, k2j, h2j, pv[NR];
-  __device__ __forceinline__ void load(const TUpdVec& v, double* const (&prow)[NR], int j) {
-    kj = v.Kv[j];
-    hj = v.Hv[j];
-    aj = v.av[j];
-    k2j = (RD == 3) ? v.K2[j] : 0.0;
-    h2j = (RD == 3) ? v.H2[j] : 0.0;
-#pragma unroll
-    for (int m = 0; m < NR; m++) pv[m] = prow[m][j];
-  }
-  __device__ __forceinline__ void apply(const double2 (&wr)[NR], const double2 (&kr)[NR], const double (&w2r)[NR], const double (&k2r)[NR],
-                                        const double (&ar)[NR], double* const (&prow)[NR], const int (&jmax)[NR], const int (&ii)[NR], double* Pbb,
-                                        int j) const {
-    // all NR elements first (independent FMA chains interleave), then the guarded stores: no divergent region per element
-    double nv[NR];
-#pragma unroll
-    for (int m = 0; m < NR; m++) {
-      const double d = rank_delta<RD>(wr[m], kr[m], w2r[m], k2r[m], kj, hj, k2j, h2j);
-      const double u = fma(-ar[m], aj, 1.0);
-      nv[m] = fma(d, u, pv[m]);
-    }
-#pragma unroll
-    for (int m = 0; m < NR; m++) {
-      const bool ok = j <= jmax[m];
-      if (ok) prow[m][j] = nv[m];
-      if (ok && ii[m] < 16) Pbb[j * PBS + ii[m]] = nv[m];
-    }
-  }
-};
-
 // rows of [P_bb; P_fb]: one row per lane, three rows per pass; column vectors are warp broadcasts (out of line: see base_pfb)
 template <int RD>
 static __device__ __noinline__ void base_rank(TUpdVec v, double* Pbb, double* Pfb, int npad, int lane) {
@@ -564,16 +530,33 @@ static __device__ __noinline__ void base_rank(TUpdVec v, double* Pbb, double* Pf
       prow[m] = (ii[m] < 16) ? Pbb + ii[m] * PBS : Pfb + (ii[m] - 16) * 17;
       jmax[m] = valid ? (ii[m] < 16 ? ii[m] : 15) : -1;
     }
-    // column j of the three rows, software-pipelined over pairs of columns (loads of column j+1 ahead of the FMAs of column j)
-    BaseCol<RD, NR> ca, cb;
-    ca.load(v, prow, 0);
-#pragma unroll 1
-    for (int j = 0; j < 16; j += 2) {
-      cb.load(v, prow, j + 1);
-      ca.apply(wr, kr, w2r, k2r, ar, prow, jmax, ii, Pbb, j);
-      if (j + 2 < 16) ca.load(v, prow, j + 2);
-      cb.apply(wr, kr, w2r, k2r, ar, prow, jmax, ii, Pbb, j + 1);
+    // the three rows go to registers first (immediate-offset loads, no per-column address arithmetic), then 16 fully
+    // unrolled columns: column vectors are warp broadcasts, the three rows give independent FMA chains
+    double pr[NR][16];
+#pragma unroll
+    for (int m = 0; m < NR; m++)
+#pragma unroll
+      for (int j = 0; j < 16; j++) pr[m][j] = prow[m][j];
+#pragma unroll
+    for (int j = 0; j < 16; j++) {
+      const double2 kj = v.Kv[j], hj = v.Hv[j];
+      const double aj = v.av[j];
+      const double k2j = (RD == 3) ? v.K2[j] : 0.0, h2j = (RD == 3) ? v.H2[j] : 0.0;
+#pragma unroll
+      for (int m = 0; m < NR; m++) {
+        const double d = rank_delta<RD>(wr[m], kr[m], w2r[m], k2r[m], kj, hj, k2j, h2j);
+        const double u = fma(-ar[m], aj, 1.0);
+        pr[m][j] = fma(d, u, pr[m][j]);
+      }
     }
+#pragma unroll
+    for (int m = 0; m < NR; m++)
+#pragma unroll
+      for (int j = 0; j < 16; j++) {
+        const bool ok = j <= jmax[m];
+        if (ok) prow[m][j] = pr[m][j];
+        if (ok && ii[m] < 16) Pbb[j * PBS + ii[m]] = pr[m][j];
+      }
   }
 }
 
