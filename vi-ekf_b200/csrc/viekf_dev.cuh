@@ -67,8 +67,17 @@ enum { SM_ZV = 0 /*2 x 8, double buffered*/, SM_HC = 16 /*18*/, SM_RES = 34 /*4*
 // ------------------------------------------------------------------------------------------------------------------
 // PROP
 // ------------------------------------------------------------------------------------------------------------------
+// Called by the whole last warp of the group: the zero fill of the continuous blocks is spread over its lanes, the
+// (serial) dynamics and Jacobian entries are written by its last lane.
 template <int G>
 __device__ void base_dynamics(const Ctx<G>& c, const KParams& p, const double* ub) {
+  {
+    const int lane = c.tid & 31;
+    for (int i = lane; i < 144; i += 32) c.Ac[i] = 0.0;
+    for (int i = lane; i < 54; i += 32) c.Gb[i] = 0.0;
+    __syncwarp();
+    if (lane != 31) return;
+  }
   const double* x = c.x;
   V3 vel = ld3(x + 3);
   Q4 q = ldq(x + 6);
@@ -90,10 +99,8 @@ __device__ void base_dynamics(const Ctx<G>& c, const KParams& p, const double* u
   dx[3] = vd.x; dx[4] = vd.y; dx[5] = vd.z;
   dx[6] = om.x; dx[7] = om.y; dx[8] = om.z;
   for (int i = 9; i < 16; i++) dx[i] = 0.0;
-  double* A = c.Ac;  // 9 x 16 row-major (rows POS, VEL, ATT of the continuous A)
-  for (int i = 0; i < 144; i++) A[i] = 0.0;
+  double* A = c.Ac;  // 9 x 16 row-major (rows POS, VEL, ATT of the continuous A), zero-filled above
   double* Gb = c.Gb;  // 9 x 6
-  for (int i = 0; i < 54; i++) Gb[i] = 0.0;
   const double sv[9] = {0, -vel.z, vel.y, vel.z, 0, -vel.x, -vel.y, vel.x, 0};
   const double so[9] = {0, -om.z, om.y, om.z, 0, -om.x, -om.y, om.x, 0};
   const double sg[9] = {0, -gB.z, gB.y, gB.z, 0, -gB.x, -gB.y, gB.x, 0};
@@ -298,7 +305,7 @@ __device__ __forceinline__ bool prop_discretise(Ctx<G>& c, const KParams& p, con
     ub[0] = a.x; ub[1] = a.y; ub[2] = a.z; ub[3] = g.x; ub[4] = g.y; ub[5] = g.z;
   }
   // ---- phase A: continuous dynamics and Jacobian blocks ----
-  if (c.tid == G - 1) base_dynamics(c, p, ub);
+  if (c.tid >= G - 32) base_dynamics(c, p, ub);
   for (int i = c.tid; i < len; i += G) feature_dynamics(c, p, ub, i);
   c.sync();
   // ---- phase B: discretisation, one row of [A_d | G_d] per task (vi_ekf.cpp:302-303) ----

@@ -24,7 +24,7 @@ namespace vk {
 constexpr int PBS = 18;  // row stride of P_bb: even (16-byte rows for vector loads), 2-way conflicts at worst for row-per-lane access
 
 struct TLayout {
-  int x, Pbb, Pfb, lam, dx, Abd, AbT, T, Ac, Gb, Afd, Gd, Y, upd, small, ids, smap, evb, fixk, fixv, total, TR;
+  int x, Pbb, Pfb, lam, dx, Abd, AbT, T, Ac, Gb, Afd, Gd, Y, upd, small, ids, smap, evb, fixk, fixv, zvr, total, TR;
 };
 __host__ __device__ inline TLayout make_tlayout(int N) {
   TLayout L;
@@ -54,6 +54,7 @@ __host__ __device__ inline TLayout make_tlayout(int N) {
   L.evb = o;   o += 64;                  // two staged viekf_event records (31 doubles each): the current and the next event
   L.fixk = o;  o += ev2(NP / 2 + 1);     // pending fix_depth covariance corrections per feature: kind (int32) ...
   L.fixv = o;  o += NP;                  // ... and value
+  L.zvr = o;   o += 64;                  // ring of 8 resolved value blocks (8 doubles each): event r reads block r & 7
   L.total = ev2(o);
   return L;
 }
@@ -94,18 +95,23 @@ struct TCtx : Ctx<32 * (TW + 1)> {
   bool tile;    // this thread owns a tile of the (capacity) grid
   bool basew;   // this thread belongs to the base warp
   int lane;
-  // the next event's per-instance values are resolved (Philox noise, ~400 instructions on 8 lanes) by a warp that has slack
-  // in the current event: the base warp in propagate phase D2, warp 1 in the rank-update phase; otherwise by warp 1 up front
-  int64_t next_e;    // event to resolve, -1 = none
+  // per-instance values (Philox noise: a ~400-instruction dependent chain per value) are resolved four events at a time --
+  // every fourth event, one warp resolves events e+1..e+4 on 4 x 8 lanes -- by a warp that has slack in that event: the base
+  // warp in propagate phase D2, warp 1 in the rank-update phase; otherwise by warp 1 up front
+  int64_t next_e;    // first event to resolve in this event's slot, -1 = none
   int64_t ginst;
-  double* zv_next;
+  double* zvr;       // ring of 8 value blocks
   bool resolved;
   PH_DECL
 };
 
 template <int TW>
 __device__ __forceinline__ void resolve_next(TCtx<TW>& c, const KParams& p, int first_tid) {
-  if (c.next_e >= 0 && c.tid >= first_tid && c.tid < first_tid + 8) resolve_values(p, c.next_e, c.b, c.ginst, c.tid - first_tid, c.zv_next);
+  if (c.next_e >= 0 && c.tid >= first_tid && c.tid < first_tid + 32) {
+    const int l = c.tid - first_tid;
+    const int64_t ev = c.next_e + (l >> 3);
+    if (ev < p.ev_first + p.ev_count) resolve_values(p, ev, c.b, c.ginst, l & 7, c.zvr + 8 * (int)((ev - p.ev_first) & 7));
+  }
   c.resolved = true;
 }
 
@@ -1024,6 +1030,7 @@ __global__ void __launch_bounds__(32 * (TW + 1) * FPC, (FPC == 1 ? 4 : (FPC == 2
   c.smap = (int*)(base + L.smap);
   c.fixk = (int*)(base + L.fixk);
   c.fixv = base + L.fixv;
+  c.zvr = base + L.zvr;
   c.tcur = c.sm + SM_T;
   double* evb = base + L.evb;
   constexpr int EVW = (int)(sizeof(viekf_event) / sizeof(double));
@@ -1067,7 +1074,7 @@ __global__ void __launch_bounds__(32 * (TW + 1) * FPC, (FPC == 1 ? 4 : (FPC == 2
       }
       tile_load(c, gP, Pt, len0, false);
     }
-    if (p.ev_count > 0 && c.tid < 8) resolve_values(p, p.ev_first, b, ginst, c.tid, c.sm + SM_ZV);
+    if (p.ev_count > 0 && c.tid < 8) resolve_values(p, p.ev_first, b, ginst, c.tid, c.zvr);
     if (p.ev_count > 0 && c.tid >= 64 && c.tid < 64 + EVW) evb[c.tid - 64] = ((const double*)(p.ev + p.ev_first))[c.tid - 64];
     PHS(c, 0)
     // ---- run the tape slice ----
@@ -1080,9 +1087,8 @@ __global__ void __launch_bounds__(32 * (TW + 1) * FPC, (FPC == 1 ? 4 : (FPC == 2
       const bool stage = (e + 1 < p.ev_first + p.ev_count) && c.tid >= 64 && c.tid < 64 + EVW;
       if (stage) ev_next = __ldg((const double*)(p.ev + e + 1) + (c.tid - 64));
       const int kind = E.kind;
-      c.zv = c.sm + SM_ZV + 8 * (int)((e - p.ev_first) & 1);
-      c.next_e = (e + 1 < p.ev_first + p.ev_count) ? e + 1 : -1;
-      c.zv_next = c.sm + SM_ZV + 8 * (int)((e + 1 - p.ev_first) & 1);
+      c.zv = c.zvr + 8 * (int)((e - p.ev_first) & 7);
+      c.next_e = (((e - p.ev_first) & 3) == 0 && e + 1 < p.ev_first + p.ev_count) ? e + 1 : -1;
       c.resolved = false;
       int result = VIEKF_MEAS_NONE;
       if (active) {
