@@ -94,6 +94,7 @@ static void fill_params(viekf_batch* h) {
       p.RbcSp[i * 3 + j] = s;
     }
   p.min_depth = c.min_depth;
+  p.depth_reset = 1.0 / (2.0 * c.min_depth);
   p.kf_thresh = c.keyframe_overlap_threshold;
   p.use_drag = c.use_drag_term;
   p.use_partial = c.use_partial_update;

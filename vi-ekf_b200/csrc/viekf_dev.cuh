@@ -210,7 +210,7 @@ template <int G>
 __device__ __forceinline__ void fix_depth_one(const Ctx<G>& c, const KParams& p, int i) {
   double* rho = c.x + 17 + 5 * i + 4;
   const int d = 16 + 3 * i + 2;
-  const double reset = 1.0 / (2.0 * p.min_depth);
+  const double reset = p.depth_reset;
   double r = *rho;
   uint32_t fl = 0;
   int nfix = 0;

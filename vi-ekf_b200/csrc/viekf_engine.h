@@ -32,6 +32,7 @@ struct KParams {
   double Rbc[9];    // q_b_c.R(), row-major
   double RbcSp[9];  // q_b_c.R() * skew(p_b_c)
   double min_depth, kf_thresh;
+  double depth_reset;  // 1 / (2 min_depth): the inverse depth fix_depth resets to (vi_ekf_helper.cpp:131), precomputed on the host
   int32_t use_drag, use_partial, use_kfreset;
   // ---- geometry of the batch ----
   int32_t N;      // NUM_FEATURES (capacity)

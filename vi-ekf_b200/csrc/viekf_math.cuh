@@ -70,8 +70,10 @@ __device__ __forceinline__ Q4 qinv(Q4 a) { return Q4{a.w, -a.x, -a.y, -a.z}; }
 __device__ __forceinline__ Q4 qexp(V3 v) {
   double n = norm(v);
   if (n > 1e-4) {
-    double s = sin(n / 2.0) / n;
-    return Q4{cos(n / 2.0), s * v.x, s * v.y, s * v.z};
+    double sn, cs;
+    sincos(n / 2.0, &sn, &cs);  // one argument reduction for both
+    const double s = sn / n;
+    return Q4{cs, s * v.x, s * v.y, s * v.z};
   }
   Q4 o{1.0, v.x / 2.0, v.y / 2.0, v.z / 2.0};
   double nn = sqrt(o.w * o.w + o.x * o.x + o.y * o.y + o.z * o.z);

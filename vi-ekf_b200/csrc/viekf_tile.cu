@@ -187,7 +187,7 @@ __device__ __forceinline__ void tile_store(const TCtx<TW>& c, double* gP, const 
 template <int TW>
 __device__ __forceinline__ void tile_fix_x(const TCtx<TW>& c, const KParams& p, int i) {
   double* rho = c.x + 17 + 5 * i + 4;
-  const double reset = 1.0 / (2.0 * p.min_depth);
+  const double reset = p.depth_reset;
   double r = *rho;
   uint32_t fl = 0;
   int nfix = 0;
