@@ -48,7 +48,7 @@ def _compare(bk, ref, idxs=None, tol=REL_TOL, tag=""):
     return worst
 
 
-@pytest.mark.parametrize("NF,steps", [(0, 40), (3, 60), (12, 72)])
+@pytest.mark.parametrize("NF,steps", [(0, 40), (3, 60), (12, 72), (35, 48)])
 def test_tape_parity_all_event_kinds(pkg, oracle_mod, NF, steps):
     cfg = _default_cfg()
     ev, idp, f, nb = tapes.consistent_tape(oracle_mod, cfg, NF, steps=steps, seed=10 + NF)

@@ -1001,7 +1001,7 @@ struct TileCore {
 // instructions at any time (the executor is instruction-fetch bound when its CTAs drift apart over the ~0.5 MB of code).
 // ------------------------------------------------------------------------------------------------------------------
 template <int TW, int FPC>
-__global__ void __launch_bounds__(32 * (TW + 1) * FPC, (FPC == 1 ? 4 : (FPC == 2 ? 2 : 1))) viekf_tile_kernel(const __grid_constant__ KParams p) {
+__global__ void __launch_bounds__(32 * (TW + 1) * FPC, (32 * (TW + 1) * FPC <= 128 ? 4 : (32 * (TW + 1) * FPC <= 256 ? 2 : 1))) viekf_tile_kernel(const __grid_constant__ KParams p) {
   extern __shared__ __align__(16) double smem[];
   constexpr int G = 32 * (TW + 1);
   const TLayout L = make_tlayout(p.N);
@@ -1179,7 +1179,8 @@ extern "C" int viekf_debug_phase_clocks(unsigned long long* clk, unsigned long l
 }
 #endif
 
-int tile_warps_for(int N) { return (N >= 7 && N <= 26) ? 3 : 0; }
+// 91 tiles (N <= 26) fit three tile warps, 171 tiles (N <= 36) six
+int tile_warps_for(int N) { return (N >= 7 && N <= 26) ? 3 : ((N >= 27 && N <= 36) ? 6 : 0); }
 
 template <int TW, int FPC>
 static cudaError_t launch_tile_fpc(const KParams& p, int sm_count, cudaStream_t stream) {
@@ -1209,18 +1210,23 @@ static cudaError_t launch_tile_fpc(const KParams& p, int sm_count, cudaStream_t 
 }
 
 cudaError_t launch_tile(const KParams& p, int sm_count, cudaStream_t stream) {
-  constexpr int TW = 3;
-  if (tile_warps_for(p.N) != TW) return cudaErrorInvalidValue;
-  // filters per CTA in event lock-step: 3 (384 threads, 168 registers each: the 72-register tile plus a schedule with loads
-  // in flight; 4 x 128 registers spills on the hot path); small batches spread over the SMs first
-  int fpc = (p.B < 3 * (int64_t)sm_count) ? 1 : 3;
+  const int tw = tile_warps_for(p.N);
+  if (tw == 0) return cudaErrorInvalidValue;
+  // filters per CTA in event lock-step.  TW = 3: 3 (384 threads, 168 registers each: the 72-register tile plus a schedule with
+  // loads in flight; 4 x 128 registers spills on the hot path).  TW = 6: 2 (448 threads, 144 registers).  Small batches spread
+  // over the SMs first.
+  const int full = (tw == 3) ? 3 : 2;
+  int fpc = (p.B < full * (int64_t)sm_count) ? 1 : full;
   if (const char* s = getenv("VIEKF_TILE_FPC")) fpc = atoi(s);
-  switch (fpc) {
-    case 1: return launch_tile_fpc<TW, 1>(p, sm_count, stream);
-    case 2: return launch_tile_fpc<TW, 2>(p, sm_count, stream);
-    case 3: return launch_tile_fpc<TW, 3>(p, sm_count, stream);
-    default: return launch_tile_fpc<TW, 4>(p, sm_count, stream);
+  if (tw == 3) {
+    switch (fpc) {
+      case 1: return launch_tile_fpc<3, 1>(p, sm_count, stream);
+      case 2: return launch_tile_fpc<3, 2>(p, sm_count, stream);
+      case 3: return launch_tile_fpc<3, 3>(p, sm_count, stream);
+      default: return launch_tile_fpc<3, 4>(p, sm_count, stream);
+    }
   }
+  return fpc >= 2 ? launch_tile_fpc<6, 2>(p, sm_count, stream) : launch_tile_fpc<6, 1>(p, sm_count, stream);
 }
 
 }  // namespace vk
