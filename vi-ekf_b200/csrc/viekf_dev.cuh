@@ -1082,9 +1082,9 @@ __device__ __forceinline__ int ev_update(Ctx<G>& c, const KParams& p, const viek
     H.col[1] = H.col[0] + 1;
     V3 ze, T0, T1;
     zeta_T(ldq(x + 17 + 5 * fi), ze, T0, T1);
-    const double ez = ze.z;
-    H.res[0] = zv[0] - (p.fl[0] * ze.x / ez + p.cc[0]);
-    H.res[1] = zv[1] - (p.fl[1] * ze.y / ez + p.cc[1]);
+    const double iez = 1.0 / ze.z;  // one reciprocal for the four divisions by e_z^T zeta of vi_ekf_meas.cpp:358-366 (1 ulp each)
+    H.res[0] = zv[0] - (p.fl[0] * ze.x * iez + p.cc[0]);
+    H.res[1] = zv[1] - (p.fl[1] * ze.y * iez + p.cc[1]);
     const double zz[3] = {ze.x, ze.y, ze.z};
     const double sk[9] = {0, -ze.z, ze.y, ze.z, 0, -ze.x, -ze.y, ze.x, 0};
     const double Tm[6] = {T0.x, T1.x, T0.y, T1.y, T0.z, T1.z};
@@ -1092,7 +1092,7 @@ __device__ __forceinline__ int ev_update(Ctx<G>& c, const KParams& p, const viek
     for (int a = 0; a < 2; a++) {
       double fb[3], fbs[3];
 #pragma unroll
-      for (int k = 0; k < 3; k++) fb[k] = (1.0 / ez) * p.fl[a] * (((k == 2) ? zz[a] : 0.0) / ez - (a == k ? 1.0 : 0.0));
+      for (int k = 0; k < 3; k++) fb[k] = iez * p.fl[a] * (((k == 2) ? zz[a] : 0.0) * iez - (a == k ? 1.0 : 0.0));
 #pragma unroll
       for (int k = 0; k < 3; k++) fbs[k] = fb[0] * sk[k] + fb[1] * sk[3 + k] + fb[2] * sk[6 + k];
 #pragma unroll

@@ -117,6 +117,11 @@ __device__ __forceinline__ void resolve_next(TCtx<TW>& c, const KParams& p, int 
 
 #define PT(r, c) Pt[(r) * 6 + (c)]
 
+#ifndef VIEKF_LOCKSTEP
+#define VIEKF_LOCKSTEP 1
+#endif
+constexpr int LOCKSTEP = VIEKF_LOCKSTEP;  // events between CTA-wide barriers (power of two)
+
 
 // Base-warp threads own no tile: their Pt is all zeros for the whole launch.  Re-zeroing it at the end of a base-warp-only
 // section makes the 72 tile registers dead inside that section, so its loops get the full register budget (loads batched
@@ -1127,8 +1132,10 @@ __global__ void __launch_bounds__(32 * (TW + 1) * FPC, (32 * (TW + 1) * FPC <= 1
       }
       if (stage) evb[32 * (int)((e + 1 - p.ev_first) & 1) + (c.tid - 64)] = ev_next;
       PH(c, 16 + kind)
-      if (FPC > 1)
-        __syncthreads();  // all filters of the CTA start the next event together
+      // the filters of a CTA re-align every LOCKSTEP events (all start the next event together); in between only the group
+      // synchronises, so a filter that finishes an event early (gated update, fewer live features) is not held back each time
+      if (FPC > 1 && ((int)(e - p.ev_first) & (LOCKSTEP - 1)) == LOCKSTEP - 1)
+        __syncthreads();
       else
         c.sync();
       PH(c, 16 + kind + 32)
