@@ -76,8 +76,8 @@ __device__ __forceinline__ Q4 qexp(V3 v) {
     return Q4{cs, s * v.x, s * v.y, s * v.z};
   }
   Q4 o{1.0, v.x / 2.0, v.y / 2.0, v.z / 2.0};
-  double nn = sqrt(o.w * o.w + o.x * o.x + o.y * o.y + o.z * o.z);
-  return Q4{o.w / nn, o.x / nn, o.y / nn, o.z / nn};
+  const double inn = 1.0 / sqrt(o.w * o.w + o.x * o.x + o.y * o.y + o.z * o.z);  // one reciprocal for the four components
+  return Q4{o.w * inn, o.x * inn, o.y * inn, o.z * inn};
 }
 __device__ __forceinline__ V3 qlog(Q4 q) {
   V3 v = mk3(q.x, q.y, q.z);
