@@ -152,10 +152,13 @@ def run_reference(args, rank, world):
 
 
 def workload_config():
-    return {"workload": f"BASELINE configs[3]: {B_PER_GPU} filters x {N_FEAT} features per GPU, 200 Hz IMU / 30 Hz camera, ACC-drag every IMU "
+    name = "BASELINE configs[3]" if (N_FEAT, B_PER_GPU) == (25, 262144) else (
+        "BASELINE configs[4] per-GPU shard" if (N_FEAT, B_PER_GPU) == (35, 1048576) else "non-default size of the configs[3] workload")
+    gb = B_PER_GPU * (17 + 5 * N_FEAT + (16 + 3 * N_FEAT) * (17 + 3 * N_FEAT) // 2) * 8 / 1e9
+    return {"workload": f"{name}: {B_PER_GPU} filters x {N_FEAT} features per GPU, 200 Hz IMU / 30 Hz camera, ACC-drag every IMU "
                         f"sample, ALT 25 Hz, keep_only_features churn, Philox per-instance noise; step = {IMU_PER_STEP} IMU samples per filter",
             "filters_per_gpu": B_PER_GPU, "features": N_FEAT, "imu_per_step": IMU_PER_STEP,
-            "l2": "per-step working set 9.2 GB per GPU (x, P of every filter) >> 126 MB L2, no flush needed"}
+            "l2": f"per-step working set {gb:.1f} GB per GPU (x, P of every filter) >> 126 MB L2, no flush needed"}
 
 
 def run_gpu(args, rank, world, local_rank):
@@ -328,8 +331,10 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--filters", type=int, default=B_PER_GPU, help="filters per GPU (default: BASELINE configs[3])")
+    ap.add_argument("--features", type=int, default=N_FEAT, help="features per filter (default 25: BASELINE configs[3]; 35 = configs[4])")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     args = ap.parse_args()
+    globals().update(N_FEAT=args.features, B_PER_GPU=args.filters, METRIC=METRIC.replace("25 features", f"{args.features} features"))
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))

@@ -190,6 +190,30 @@ int viekf_batch_clear_feature(viekf_batch* h, int32_t id);
 int viekf_batch_keep_only_features(viekf_batch* h, const int32_t* ids, int32_t n);
 int viekf_batch_keyframe_reset(viekf_batch* h);
 
+/* ---- Delayed-measurement queue: the reference's streaming call pattern (vi_ekf_meas.cpp:6-194) ------------------------
+ * The reference keeps a LEN_STATE_HIST-deep ring of (x, P, t) and a sorted measurement deque (include/vi_ekf.h:50-51,
+ * 157-181); handle_measurements rewinds the ring to just before the oldest pending measurement and replays the stored
+ * inputs and measurements.  viekf_batch_queue_enable gives the handle the same ring in HBM (len_state_hist slots of x and
+ * packed P for all B instances; VIEKF_ERR_NOMEM when it does not fit) and the same two deques on the host.  Call times and
+ * values are shared by all instances (the instances differ by their state, e.g. viekf_batch_perturb_x0), so the
+ * rewind / replay decisions are uniform over the batch while gating stays per instance.  Must be called before the
+ * first propagate.  Pass 250 / 200 for the reference's LEN_STATE_HIST / LEN_MEAS_HIST. */
+int viekf_batch_queue_enable(viekf_batch* h, int32_t len_state_hist, int32_t len_meas_hist);
+/* propagate_state(u, t, save_input) (vi_ekf.cpp:262-318) on the ring: the new state goes to the next slot, the input is
+ * pushed onto the input deque when save_input != 0.  u is one IMU sample [6] (IMU frame). */
+int viekf_batch_queue_propagate(viekf_batch* h, const double* u, double t, int32_t save_input);
+/* add_measurement (vi_ekf_meas.cpp:130-194): t < start => MEAS_INVALID, NaN in z => MEAS_NAN, FEAT with an untracked id =>
+ * init_feature now and MEAS_NEW_FEATURE, otherwise sorted insert (LIFO among equal times) and MEAS_SUCCESS.
+ * z is [zdim], R rdim x rdim column-major; *result receives the meas_result_t. */
+int viekf_batch_add_measurement(viekf_batch* h, double t, int32_t type, const double* z, int32_t zdim, const double* R,
+                                int32_t rdim, int32_t active, int32_t id, double depth, int32_t* result);
+/* handle_measurements (vi_ekf_meas.cpp:6-127).  For the k-th update() applied by this call: upd_types[k], upd_ids[k] and
+ * upd_results[k*B + b] = meas_result_t of instance b (the reference's gated_feature_ids list is {upd_ids[k] : FEAT and
+ * result == MEAS_GATED}, per instance).  cap = capacity of the three arrays in updates (any may be NULL);
+ * *n_updates receives the number applied. */
+int viekf_batch_handle_measurements(viekf_batch* h, int32_t* upd_types, int32_t* upd_ids, uint8_t* upd_results, int32_t cap,
+                                    int32_t* n_updates);
+
 /* Fused path: run a whole tape with x and P resident on chip.  results (may be NULL) is
  * [n_events x result_count] uint8 meas_result_t for instances result_first.. (row-major by instance:
  * results[(b-result_first)*n_events + e]). */

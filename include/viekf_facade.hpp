@@ -8,8 +8,10 @@
 //
 // Semantics preserved from the reference: the first propagate_state only latches the time (vi_ekf.cpp:274-279); feature
 // ids are assigned internally (vi_ekf_feat.cpp:29-31); a FEAT measurement with an untracked id initialises the feature and
-// returns MEAS_NEW_FEATURE (vi_ekf_meas.cpp:140-147); measurements are applied in order at the filter's current time, so
-// handle_measurements() has nothing left to do (the rewind/replay queue is replaced by in-order tapes).
+// returns MEAS_NEW_FEATURE (vi_ekf_meas.cpp:140-147).  Two modes: by default measurements are applied in order at the filter's
+// current time and handle_measurements() has nothing left to do; after enable_queue() the reference's
+// delayed-measurement queue is in force (vi_ekf_meas.cpp:6-194): add_measurement queues by time stamp, handle_measurements
+// rewinds the history ring and replays, exactly as the reference's streaming callers expect (src/vi_ekf_ros.cpp:174-198).
 // Errors: the reference prints to cerr or exits; here every failing ABI call throws std::runtime_error(viekf_last_error()).
 #pragma once
 #include <cmath>
@@ -61,15 +63,44 @@ class BatchVIEKF {
   // vi_ekf.cpp:157-184
   void set_x0(const double* x0, bool broadcast = true) { check(viekf_batch_set_x0(h_, x0, broadcast ? 1 : 0)); }
   // vi_ekf.cpp:262-318: u = [acc(3), gyro(3)] in the IMU frame, one column shared by all copies or [6 x B]
-  void propagate_state(const double* u, double t, bool broadcast = true) { check(viekf_batch_propagate(h_, u, broadcast ? 1 : 0, t)); }
+  void propagate_state(const double* u, double t, bool broadcast = true, bool save_input = true) {
+    if (queue_)
+      check(viekf_batch_queue_propagate(h_, u, t, save_input ? 1 : 0));  // one shared IMU sample
+    else
+      check(viekf_batch_propagate(h_, u, broadcast ? 1 : 0, t));
+  }
+  // include/vi_ekf.h:50-51: LEN_STATE_HIST / LEN_MEAS_HIST; must precede the first propagate_state
+  void enable_queue(int len_state_hist = 250, int len_meas_hist = 200) {
+    check(viekf_batch_queue_enable(h_, len_state_hist, len_meas_hist));
+    queue_ = true;
+  }
+  bool queue_enabled() const { return queue_; }
   // vi_ekf_meas.cpp:130-194 + 196-278; returns one meas_result_t per copy
-  std::vector<uint8_t> add_measurement(double /*t*/, const double* z, int zdim, measurement_type_t type, const double* R, int rdim,
+  std::vector<uint8_t> add_measurement(double t, const double* z, int zdim, measurement_type_t type, const double* R, int rdim,
                                        bool active = false, int id = -1, double depth = NAN, bool broadcast = true) {
     std::vector<uint8_t> res((size_t)B_);
+    if (queue_) {
+      int32_t r = 0;
+      check(viekf_batch_add_measurement(h_, t, (int32_t)type, z, zdim, R, rdim, active ? 1 : 0, id, depth, &r));
+      res.assign((size_t)B_, (uint8_t)r);
+      return res;
+    }
     check(viekf_batch_update(h_, (int32_t)type, z, zdim, broadcast ? 1 : 0, R, rdim, active ? 1 : 0, id, depth, res.data()));
     return res;
   }
-  void handle_measurements() {}  // in-order application: nothing is queued
+  // vi_ekf_meas.cpp:6-127; gated_feature_ids (may be null) receives the FEAT ids gated for copy `instance`
+  void handle_measurements(std::vector<int>* gated_feature_ids = nullptr, int64_t instance = 0) {
+    if (gated_feature_ids) gated_feature_ids->clear();
+    if (!queue_) return;  // in-order application: nothing is queued
+    const int cap = 512;
+    std::vector<int32_t> ty(cap), ids(cap);
+    std::vector<uint8_t> res((size_t)cap * (size_t)B_);
+    int32_t n = 0;
+    check(viekf_batch_handle_measurements(h_, ty.data(), ids.data(), res.data(), cap, &n));
+    if (gated_feature_ids)
+      for (int k = 0; k < n && k < cap; k++)
+        if (ty[k] == VIEKF_FEAT && res[(size_t)k * B_ + instance] == VIEKF_MEAS_GATED) gated_feature_ids->push_back(ids[k]);
+  }
   // vi_ekf_feat.cpp:6-142
   std::vector<uint8_t> init_feature(const double* pixel, int id, double depth = NAN, bool broadcast = true) {
     std::vector<uint8_t> ok((size_t)B_);
@@ -114,6 +145,7 @@ class BatchVIEKF {
     if (rc != 0) throw std::runtime_error(std::string("viekf: ") + viekf_last_error());
   }
   viekf_batch* h_ = nullptr;
+  bool queue_ = false;
   int64_t B_;
   int N_;
 };
@@ -123,7 +155,7 @@ class VIEKF : public BatchVIEKF {
  public:
   explicit VIEKF(const viekf_config& cfg, int num_features = 12 /* reference default NUM_FEATURES */, int device = 0)
       : BatchVIEKF(cfg, 1, num_features, device) {}
-  void propagate_state(const double (&u)[6], double t, bool /*save_input*/ = true) { BatchVIEKF::propagate_state(u, t, true); }
+  void propagate_state(const double (&u)[6], double t, bool save_input = true) { BatchVIEKF::propagate_state(u, t, true, save_input); }
   meas_result_t add_measurement(double t, const double* z, int zdim, measurement_type_t type, const double* R, int rdim, bool active = false,
                                 int id = -1, double depth = NAN) {
     return (meas_result_t)BatchVIEKF::add_measurement(t, z, zdim, type, R, rdim, active, id, depth, true)[0];
@@ -132,8 +164,7 @@ class VIEKF : public BatchVIEKF {
 #ifdef VIEKF_FACADE_HAS_EIGEN
   // the reference's own signatures (include/vi_ekf.h:294-309)
   void propagate_state(const Eigen::Matrix<double, 6, 1>& u, double t, bool save_input = true) {
-    (void)save_input;
-    BatchVIEKF::propagate_state(u.data(), t, true);
+    BatchVIEKF::propagate_state(u.data(), t, true, save_input);
   }
   meas_result_t add_measurement(double t, const Eigen::VectorXd& z, measurement_type_t type, const Eigen::MatrixXd& R, bool active = false,
                                 int id = -1, double depth = NAN) {

@@ -123,6 +123,10 @@ def load_library():
         "viekf_batch_clear_feature": (i32, [vp, i32]),
         "viekf_batch_keep_only_features": (i32, [vp, vp, i32]),
         "viekf_batch_keyframe_reset": (i32, [vp]),
+        "viekf_batch_queue_enable": (i32, [vp, i32, i32]),
+        "viekf_batch_queue_propagate": (i32, [vp, vp, dbl, i32]),
+        "viekf_batch_add_measurement": (i32, [vp, dbl, i32, vp, i32, vp, i32, i32, i32, dbl, C.POINTER(i32)]),
+        "viekf_batch_handle_measurements": (i32, [vp, vp, vp, vp, i32, C.POINTER(i32)]),
         "viekf_batch_run_tape": (i32, [vp, C.POINTER(Tape), vp, i64, i64]),
         "viekf_batch_upload_tape": (i32, [vp, C.POINTER(Tape), C.POINTER(vp)]),
         "viekf_batch_free_tape": (None, [vp, vp]),

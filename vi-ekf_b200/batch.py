@@ -132,6 +132,37 @@ class BatchVIEKF:
     def keyframe_reset(self):
         self._chk(self.L.viekf_batch_keyframe_reset(self.h))
 
+    # ---- streaming path: the reference's delayed-measurement queue (vi_ekf_meas.cpp:6-194) --------------
+    def enable_queue(self, len_state_hist=250, len_meas_hist=200):
+        """History ring + measurement deque (include/vi_ekf.h:50-51); afterwards propagate_state(save_input=...),
+        add_measurement and handle_measurements follow the reference's rewind/replay semantics."""
+        self._chk(self.L.viekf_batch_queue_enable(self.h, int(len_state_hist), int(len_meas_hist)))
+        self._queue = True
+
+    def queue_propagate_state(self, u, t, save_input=True):
+        u = np.ascontiguousarray(u, dtype=np.float64)
+        assert u.shape == (6,)
+        self._chk(self.L.viekf_batch_queue_propagate(self.h, _p(u), float(t), int(bool(save_input))))
+
+    def add_measurement(self, t, z, mtype, R, active=False, id=-1, depth=float("nan")):
+        """Returns the meas_result_t of add_measurement (uniform over the batch)."""
+        z = np.ascontiguousarray(z, dtype=np.float64).ravel()
+        R = np.asfortranarray(np.atleast_2d(np.asarray(R, dtype=np.float64)))
+        res = C.c_int32(-1)
+        self._chk(self.L.viekf_batch_add_measurement(self.h, float(t), int(mtype), _p(z), z.size, _p(R), R.shape[0], int(bool(active)),
+                                                     int(id), float(depth), C.byref(res)))
+        return res.value
+
+    def handle_measurements(self, cap=256):
+        """Returns (types[k], ids[k], results[k, B]) of the updates applied by this call."""
+        ty = np.zeros(cap, dtype=np.int32)
+        ids = np.zeros(cap, dtype=np.int32)
+        res = np.zeros((cap, self.B), dtype=np.uint8)
+        n = C.c_int32(0)
+        self._chk(self.L.viekf_batch_handle_measurements(self.h, _p(ty), _p(ids), _p(res), cap, C.byref(n)))
+        k = min(n.value, cap)
+        return ty[:k], ids[:k], res[:k]
+
     # ---- fused path -----------------------------------------------------------------------------------
     def _mk_tape(self, events, id_pool, values, seed=0, bias_range=None):
         events = np.ascontiguousarray(events, dtype=abi.EVENT_DTYPE)

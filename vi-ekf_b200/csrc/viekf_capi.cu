@@ -8,6 +8,8 @@
 #include <stdlib.h>
 #include <string.h>
 #include <algorithm>
+#include <array>
+#include <deque>
 #include <string>
 #include <vector>
 #include "viekf_engine.h"
@@ -27,8 +29,28 @@ struct viekf_dev_tape {
   double bias_range[6] = {0, 0, 0, 0, 0, 0};
 };
 
+// Delayed-measurement queue of the streaming call pattern (vi_ekf_meas.cpp:6-194): the (x, P) history ring lives in HBM
+// (the handle's state pointers kp.x / kp.P always address slot i), the time ring and the two deques on the host.
+struct QueuedMeas {
+  double t, z[4], R[9], depth;
+  int32_t type, zdim, rdim, active, id;
+  bool handled;
+};
+struct MeasQueue {
+  int H = 0, MH = 0, i = 0;
+  double* rx = nullptr;  // [H][B][xs]
+  double* rP = nullptr;  // [H][B][ps]
+  std::vector<double> t;  // t_[slot]
+  double start_t = NAN;
+  std::deque<std::pair<double, std::array<double, 6>>> u;  // front = newest; body-frame inputs
+  std::deque<QueuedMeas> z;                                 // front = newest
+};
+
 struct viekf_batch {
   viekf_config cfg;
+  MeasQueue* q = nullptr;
+  double* x_main = nullptr;  // the allocations kp.x / kp.P pointed to before the ring took over
+  double* P_main = nullptr;
   int64_t B = 0;
   int32_t N = 0;
   int device = 0;
@@ -197,6 +219,13 @@ void viekf_batch_destroy(viekf_batch* h) {
   if (!h) return;
   cudaSetDevice(h->device);
   if (h->stream) cudaStreamSynchronize(h->stream);
+  if (h->q) {
+    cudaFree(h->q->rx);
+    cudaFree(h->q->rP);
+    h->kp.x = h->x_main;
+    h->kp.P = h->P_main;
+    delete h->q;
+  }
   cudaFree(h->kp.x);
   cudaFree(h->kp.P);
   cudaFree(h->kp.meta);
@@ -215,6 +244,17 @@ void viekf_batch_destroy(viekf_batch* h) {
 int viekf_batch_reset(viekf_batch* h) {
   if (!h) return fail(VIEKF_ERR_ARG, "null handle");
   CK(cudaSetDevice(h->device));
+  if (MeasQueue* q = h->q) {  // back to slot 0 of a zeroed ring with empty deques
+    CK(cudaMemsetAsync(q->rx, 0, sizeof(double) * h->kp.xs * h->B * q->H, h->stream));
+    CK(cudaMemsetAsync(q->rP, 0, sizeof(double) * h->kp.ps * h->B * q->H, h->stream));
+    q->i = 0;
+    h->kp.x = q->rx;
+    h->kp.P = q->rP;
+    q->t.assign(q->H, NAN);
+    q->start_t = NAN;
+    q->u.clear();
+    q->z.clear();
+  }
   CK(vk::launch_reset(h->kp, h->stream));
   CK(cudaStreamSynchronize(h->stream));
   return VIEKF_OK;
@@ -457,6 +497,248 @@ int viekf_batch_keyframe_reset(viekf_batch* h) {
   if (!h) return fail(VIEKF_ERR_ARG, "null handle");
   viekf_event e = blank_event(VIEKF_EV_KFRESET);
   return run_single_event(h, e, nullptr, 0, 1, nullptr);
+}
+
+// ---- delayed-measurement queue (vi_ekf_meas.cpp:6-194) ------------------------------------------------------------
+__global__ void set_time_kernel(FilterMeta* m, int64_t B, double t) {
+  const int64_t b = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (b < B) m[b].t = t;
+}
+
+// q.rota(v) on the host, the formula of viekf_math.cuh rota() (reference quat.h:377-391)
+static void host_rota(const double* q, const double* v, double* o) {
+  const double b[3] = {q[1], q[2], q[3]};
+  const double t[3] = {2.0 * (v[1] * b[2] - v[2] * b[1]), 2.0 * (v[2] * b[0] - v[0] * b[2]), 2.0 * (v[0] * b[1] - v[1] * b[0])};
+  o[0] = v[0] - q[0] * t[0] + (t[1] * b[2] - t[2] * b[1]);
+  o[1] = v[1] - q[0] * t[1] + (t[2] * b[0] - t[0] * b[2]);
+  o[2] = v[2] - q[0] * t[2] + (t[0] * b[1] - t[1] * b[0]);
+}
+
+static void queue_select_slot(viekf_batch* h, int slot) {
+  MeasQueue* q = h->q;
+  q->i = slot;
+  h->kp.x = q->rx + (size_t)slot * h->kp.xs * h->B;
+  h->kp.P = q->rP + (size_t)slot * h->kp.ps * h->B;
+}
+
+int viekf_batch_queue_enable(viekf_batch* h, int32_t len_state_hist, int32_t len_meas_hist) {
+  if (!h || len_state_hist < 2 || len_meas_hist < 1) return fail(VIEKF_ERR_ARG, "queue_enable: bad argument");
+  if (h->q) return fail(VIEKF_ERR_ARG, "queue_enable: already enabled");
+  CK(cudaSetDevice(h->device));
+  std::vector<FilterMeta> m;
+  if (int rc = fetch_meta(h, 0, 1, m)) return rc;
+  if (m[0].started) return fail(VIEKF_ERR_ARG, "queue_enable: must precede the first propagate");
+  MeasQueue* q = new MeasQueue();
+  q->H = len_state_hist;
+  q->MH = len_meas_hist;
+  q->t.assign(q->H, NAN);
+  const size_t xb = sizeof(double) * h->kp.xs * h->B, pb = sizeof(double) * h->kp.ps * h->B;
+  cudaError_t e = cudaMalloc(&q->rx, xb * q->H);
+  if (e == cudaSuccess) e = cudaMalloc(&q->rP, pb * q->H);
+  if (e != cudaSuccess) {
+    cudaFree(q->rx);
+    cudaFree(q->rP);
+    delete q;
+    cudaGetLastError();
+    return fail(VIEKF_ERR_NOMEM, "queue_enable: the history ring does not fit in device memory", e);
+  }
+  // the reference's slots start as zeros except slot 0 (vi_ekf.cpp:18-155)
+  CK(cudaMemsetAsync(q->rx, 0, xb * q->H, h->stream));
+  CK(cudaMemsetAsync(q->rP, 0, pb * q->H, h->stream));
+  CK(cudaMemcpyAsync(q->rx, h->kp.x, xb, cudaMemcpyDeviceToDevice, h->stream));
+  CK(cudaMemcpyAsync(q->rP, h->kp.P, pb, cudaMemcpyDeviceToDevice, h->stream));
+  CK(cudaStreamSynchronize(h->stream));
+  h->x_main = h->kp.x;
+  h->P_main = h->kp.P;
+  h->q = q;
+  queue_select_slot(h, 0);
+  return VIEKF_OK;
+}
+
+// propagate_state(u, t, save_input) on the ring (vi_ekf.cpp:262-318)
+static int queue_propagate_impl(viekf_batch* h, const double* u, double t, bool save_input) {
+  MeasQueue* q = h->q;
+  if (save_input) {
+    std::array<double, 6> ub;
+    host_rota(h->cfg.q_b_u, u, ub.data());
+    host_rota(h->cfg.q_b_u, u + 3, ub.data() + 3);
+    q->u.push_front({t, ub});
+  }
+  viekf_event e = blank_event(VIEKF_EV_PROP);
+  e.t = t;
+  bool advance = false;
+  if (std::isnan(q->start_t)) {  // first call latches the time (vi_ekf.cpp:274-279)
+    q->start_t = t;
+    q->t[q->i] = t;
+  } else {
+    const double dt = t - q->t[q->i];
+    advance = !(fabs(dt) < 1e-6) && !(dt < 0);  // vi_ekf.cpp:281-290
+  }
+  if (advance) {
+    // x_[ip] receives the live entries only, P_[ip] is assigned whole (vi_ekf.cpp:301,304): copy the live prefixes of slot i
+    // to slot ip and propagate in place there; what slot ip held beyond them stays, as in the reference.
+    std::vector<FilterMeta> m;
+    if (int rc = fetch_meta(h, 0, 1, m)) return rc;
+    const int len = m[0].len, n = 16 + 3 * len;
+    const int ip = (q->i + 1) % q->H;
+    const double* sx = h->kp.x;
+    const double* sP = h->kp.P;
+    queue_select_slot(h, ip);
+    CK(cudaMemcpy2DAsync(h->kp.x, sizeof(double) * h->kp.xs, sx, sizeof(double) * h->kp.xs, sizeof(double) * (17 + 5 * len), h->B,
+                         cudaMemcpyDeviceToDevice, h->stream));
+    CK(cudaMemcpy2DAsync(h->kp.P, sizeof(double) * h->kp.ps, sP, sizeof(double) * h->kp.ps, sizeof(double) * (n * (n + 1) / 2), h->B,
+                         cudaMemcpyDeviceToDevice, h->stream));
+    q->t[ip] = t;
+  }
+  return run_single_event(h, e, u, 6, 1, nullptr);
+}
+
+int viekf_batch_queue_propagate(viekf_batch* h, const double* u, double t, int32_t save_input) {
+  if (!h || !u) return fail(VIEKF_ERR_ARG, "bad argument");
+  if (!h->q) return fail(VIEKF_ERR_ARG, "queue_propagate: call viekf_batch_queue_enable first");
+  CK(cudaSetDevice(h->device));
+  return queue_propagate_impl(h, u, t, save_input != 0);
+}
+
+int viekf_batch_add_measurement(viekf_batch* h, double t, int32_t type, const double* z, int32_t zdim, const double* R, int32_t rdim,
+                                int32_t active, int32_t id, double depth, int32_t* result) {
+  if (!h || !z || !R || !result || zdim < 1 || zdim > 4 || rdim < 1 || rdim > 3 || type < 0 || type >= VIEKF_TOTAL_MEAS)
+    return fail(VIEKF_ERR_ARG, "viekf_batch_add_measurement: bad argument");
+  MeasQueue* q = h->q;
+  if (!q) return fail(VIEKF_ERR_ARG, "add_measurement: call viekf_batch_queue_enable first");
+  CK(cudaSetDevice(h->device));
+  if (t < q->start_t) {  // vi_ekf_meas.cpp:133-134
+    *result = VIEKF_MEAS_INVALID;
+    return VIEKF_OK;
+  }
+  for (int i = 0; i < zdim; i++)
+    if (z[i] != z[i]) {  // :136-137
+      *result = VIEKF_MEAS_NAN;
+      return VIEKF_OK;
+    }
+  if (type == VIEKF_FEAT && id >= 0) {  // :140-147: a new id is initialised now, in the current slot, and not queued
+    std::vector<FilterMeta> m;
+    if (int rc = fetch_meta(h, 0, 1, m)) return rc;
+    std::vector<int32_t> ids(h->N > 0 ? h->N : 1, -1);
+    if (h->N > 0) CK(cudaMemcpy(ids.data(), h->kp.ids, sizeof(int32_t) * h->N, cudaMemcpyDeviceToHost));
+    bool tracked = false;
+    for (int i = 0; i < m[0].len; i++) tracked |= (ids[i] == id);
+    if (!tracked) {
+      viekf_event e = blank_event(VIEKF_EV_INIT);
+      e.id = id;
+      e.z[4] = depth;
+      if (int rc = run_single_event(h, e, z, 2, 1, nullptr)) return rc;
+      *result = VIEKF_MEAS_NEW_FEATURE;
+      return VIEKF_OK;
+    }
+  }
+  auto it = q->z.begin();
+  while (it != q->z.end() && !(it->t < t)) ++it;  // :150-156: before the first strictly older entry
+  QueuedMeas qm;
+  memset(&qm, 0, sizeof(qm));
+  qm.t = t;
+  qm.type = type;
+  qm.zdim = zdim;
+  qm.rdim = rdim;
+  qm.active = active;
+  qm.id = id;
+  qm.depth = depth;
+  qm.handled = false;
+  for (int i = 0; i < zdim; i++) qm.z[i] = z[i];
+  for (int i = 0; i < rdim * rdim; i++) qm.R[i] = R[i];
+  q->z.insert(it, qm);
+  *result = VIEKF_MEAS_SUCCESS;
+  return VIEKF_OK;
+}
+
+int viekf_batch_handle_measurements(viekf_batch* h, int32_t* upd_types, int32_t* upd_ids, uint8_t* upd_results, int32_t cap,
+                                    int32_t* n_updates) {
+  if (!h || cap < 0) return fail(VIEKF_ERR_ARG, "bad argument");
+  MeasQueue* q = h->q;
+  if (!q) return fail(VIEKF_ERR_ARG, "handle_measurements: call viekf_batch_queue_enable first");
+  CK(cudaSetDevice(h->device));
+  int n_upd = 0;
+  if (n_updates) *n_updates = 0;
+  if (q->z.empty()) return VIEKF_OK;
+  // oldest pending measurement (vi_ekf_meas.cpp:13-22)
+  auto z_it = q->z.end() - 1;
+  while (z_it->handled && z_it != q->z.begin()) --z_it;
+  if (z_it == q->z.begin() && z_it->handled) return VIEKF_OK;
+  if (q->u.empty() || z_it->t > q->u.begin()->first) return VIEKF_OK;  // :24-28 measurement from the future
+  // newest input strictly older than the measurement (:31-39)
+  auto u_it = q->u.begin();
+  while (u_it != q->u.end() && !(z_it->t > u_it->first)) ++u_it;
+  if (u_it == q->u.end()) return VIEKF_OK;  // the reference dereferences end() here; nothing to rewind to
+  // rewind the ring to the newest state not after that input (:45-63)
+  int k = q->H;
+  int slot = -1;
+  while (k > 0) {
+    const int s = (q->i + k) % q->H;
+    if (q->t[s] <= u_it->first) {
+      slot = s;
+      break;
+    }
+    k--;
+  }
+  if (getenv("VIEKF_QUEUE_DEBUG"))
+    fprintf(stderr, "[queue] z.t=%.6f type=%d u.t=%.6f i=%d t[i]=%.6f -> slot %d nz=%zu nu=%zu\n", z_it->t, z_it->type, u_it->first, q->i,
+            q->t[q->i], slot, q->z.size(), q->u.size());
+  if (slot < 0) {  // older than the ring: the measurement is dropped
+    q->z.erase(z_it);
+    return VIEKF_OK;
+  }
+  if (slot != q->i) {
+    queue_select_slot(h, slot);
+    set_time_kernel<<<(unsigned)((h->B + 255) / 256), 256, 0, h->stream>>>(h->kp.meta, h->B, q->t[slot]);
+    CK(cudaGetLastError());
+  }
+  auto apply_update = [&](QueuedMeas& m) -> int {
+    m.handled = true;
+    viekf_event e = blank_event(VIEKF_EV_UPD);
+    e.type = m.type;
+    e.zdim = m.zdim;
+    e.rdim = m.rdim;
+    e.active = m.active;
+    e.id = m.id;
+    e.z[4] = m.depth;
+    for (int i = 0; i < m.rdim * m.rdim; i++) e.R[i] = m.R[i];
+    uint8_t* out = (upd_results && n_upd < cap) ? upd_results + (size_t)n_upd * h->B : nullptr;
+    if (int rc = run_single_event(h, e, m.z, m.zdim, 1, out)) return rc;
+    if (n_upd < cap) {
+      if (upd_types) upd_types[n_upd] = m.type;
+      if (upd_ids) upd_ids[n_upd] = m.id;
+    }
+    n_upd++;
+    return VIEKF_OK;
+  };
+  // replay (:73-117); the stored inputs are body-frame and propagate_state rotates them again, as the reference does
+  --u_it;
+  while (u_it != q->u.begin()) {
+    while (z_it->t <= u_it->first) {
+      if (q->t[q->i] < z_it->t)
+        if (int rc = queue_propagate_impl(h, u_it->second.data(), z_it->t, false)) return rc;
+      if (!z_it->handled)
+        if (int rc = apply_update(*z_it)) return rc;
+      if (z_it != q->z.begin()) {
+        --z_it;
+        while (u_it->first < z_it->t && u_it != q->u.begin()) {
+          if (int rc = queue_propagate_impl(h, u_it->second.data(), u_it->first, false)) return rc;
+          --u_it;
+        }
+      } else {
+        while (u_it != q->u.begin()) {
+          if (int rc = queue_propagate_impl(h, u_it->second.data(), u_it->first, false)) return rc;
+          --u_it;
+        }
+        break;
+      }
+    }
+  }
+  if (int rc = queue_propagate_impl(h, u_it->second.data(), u_it->first, false)) return rc;
+  while ((int)q->z.size() > q->MH) q->z.pop_back();
+  while ((int)q->u.size() > q->H) q->u.pop_back();
+  if (n_updates) *n_updates = n_upd;
+  return VIEKF_OK;
 }
 
 static int validate_tape(const viekf_tape* t) {
