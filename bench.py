@@ -151,6 +151,15 @@ def run_reference(args, rank, world):
     print(json.dumps(line), flush=True)
 
 
+def kernel_name(n):
+    """The executor launch_tape selects for N features (csrc/viekf_kernel.cu group_size_for, csrc/viekf_tile.cu tile_warps_for)."""
+    if 7 <= n <= 26:
+        return "viekf_tile_kernel<3,3> (register-tile tape executor, 3 filters per CTA)"
+    if 27 <= n <= 36:
+        return "viekf_tile_kernel<6,2> (register-tile tape executor, 2 filters per CTA)"
+    return "viekf_tape_kernel (shared-memory tape executor)"
+
+
 def workload_config():
     name = "BASELINE configs[3]" if (N_FEAT, B_PER_GPU) == (25, 262144) else (
         "BASELINE configs[4] per-GPU shard" if (N_FEAT, B_PER_GPU) == (35, 1048576) else "non-default size of the configs[3] workload")
@@ -291,7 +300,7 @@ def emit(args, pkg, world, K, W, B, ev, idp, info, slices, cfg, ms_total, ms_e2e
     except Exception:
         pass
     roofline = {
-        "bound": "fp64", "kernel": "viekf_tile_kernel<3,3> (register-tile tape executor, 3 filters per CTA)", "achieved": achieved_tf, "peak": fp64_peak, "unit": "TFLOP/s",
+        "bound": "fp64", "kernel": kernel_name(N_FEAT), "achieved": achieved_tf, "peak": fp64_peak, "unit": "TFLOP/s",
         "frac": achieved_tf / fp64_peak if fp64_peak > 0 else None, "traffic": traffic,
         "peak_source": "viekf_fp64_peak_probe (DFMA microbenchmark run by this bench; MEASURED_PEAKS.json has no FP64 figure)",
         "flops_per_launch": flops_per_launch, "avg_launch_ms": avg_launch_s * 1e3, "gated_update_fraction": gated_frac,

@@ -5,7 +5,7 @@ restatement of vi_ekf_meas.cpp:6-194 driven call for call with the same inputs.
 Tolerance: add_measurement results, applied-update order, gate results, feature ids bit-exact; x, P within 1e-9 relative.
 
 Scope: the engine keeps no covariance for dead feature slots, the reference does (P0_feat on the diagonal of all
-NUM_FEATURES slots from the constructor on, vi_ekf.cpp:60-64).  A rewind to a slot older than an init_feature therefore finds
+NUM_FEATURES slots from init() on, vi_ekf.cpp:74-80,137-143).  A rewind to a slot older than an init_feature therefore finds
 P0_feat in the reference and zeros in the engine for that feature (in both, the feature's state is whatever the old slot held:
 init_feature writes x_[i_] only, vi_ekf_feat.cpp:33-41).  The flows below initialise features in slot 0, which no rewind goes
 behind; DESIGN.md 1 lists the corner as a known divergence.
