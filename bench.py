@@ -315,6 +315,17 @@ def emit(args, pkg, world, K, W, B, ev, idp, info, slices, cfg, ms_total, ms_e2e
         "per_launch_ms": [round(v, 3) for v in per_launch_ms],
     }
     line["config"]["filters_per_gpu"] = B
+    # per-kind event rates of the whole job over the timed region (propagates/s, FEAT updates/s, ...)
+    abi = pkg.abi
+    timed = np.concatenate([ev[slices[W + i][0]:slices[W + i][1]] for i in range(K)])
+    upd = timed[timed["kind"] == abi.EV_UPD]
+    per_s = world * B / (ms_total * 1e-3)
+    line["event_rates_per_s"] = {
+        "propagate": float((timed["kind"] == abi.EV_PROP).sum() * per_s),
+        "update_feat": float((upd["type"] == abi.FEAT).sum() * per_s), "update_acc": float((upd["type"] == abi.ACC).sum() * per_s),
+        "update_alt": float((upd["type"] == abi.ALT).sum() * per_s),
+        "keep_only_features": float((timed["kind"] == abi.EV_KEEP).sum() * per_s), "init_feature": float((timed["kind"] == abi.EV_INIT).sum() * per_s),
+    }
     if nccl_ms is not None:
         line["stats_allreduce_ms"] = nccl_ms
     n = np.maximum(stats[:, 0], 1)

@@ -6,11 +6,20 @@ from tests.common import REL_TOL
 
 
 def run(pkg, verbose=False):
+    """NF = 12 runs on the register-tile executor (the kernel bench.py measures), NF = 6 on the shared-memory executor."""
+    worst = (0.0, 0.0)
+    for NF in (12, 6):
+        w = run_one(pkg, NF, verbose)
+        worst = (max(worst[0], w[0]), max(worst[1], w[1]))
+    return worst
+
+
+def run_one(pkg, NF, verbose=False):
     from oracle import oracle
     oracle.build()
     abi = pkg.abi
     cfg = abi.default_config()
-    NF, B = 6, 16
+    B = 16
     ev, idp, f, nb = tapes.consistent_tape(oracle, cfg, NF, steps=36, seed=2)
     ref = oracle.run_batch(cfg, NF, ev, idp, count=B, nthreads=4, n_buckets=nb)
     bk = pkg.BatchVIEKF(cfg, B=B, N=NF, device=0)

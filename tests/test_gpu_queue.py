@@ -4,11 +4,9 @@ restatement of vi_ekf_meas.cpp:6-194 driven call for call with the same inputs.
 
 Tolerance: add_measurement results, applied-update order, gate results, feature ids bit-exact; x, P within 1e-9 relative.
 
-Scope: the engine keeps no covariance for dead feature slots, the reference does (P0_feat on the diagonal of all
-NUM_FEATURES slots from init() on, vi_ekf.cpp:74-80,137-143).  A rewind to a slot older than an init_feature therefore finds
-P0_feat in the reference and zeros in the engine for that feature (in both, the feature's state is whatever the old slot held:
-init_feature writes x_[i_] only, vi_ekf_feat.cpp:33-41).  The flows below initialise features in slot 0, which no rewind goes
-behind; DESIGN.md 1 lists the corner as a known divergence.
+Dead feature slots: the reference's dense P carries P0_feat (+ Qx_feat per propagate) on the blocks of features that are not
+live (vi_ekf.cpp:74-80,137-143,304) and a rewind behind an init_feature brings such a block back to life
+(test_queue_new_features_behind_a_rewind); the engine keeps those rows in queue mode (csrc/viekf_capi.cu queue_dead_diag).
 """
 import numpy as np
 import pytest
@@ -19,13 +17,15 @@ from tests import tapes
 pytestmark = pytest.mark.gpu
 
 
-def _drive(pkg, oracle_mod, NF, n_imu, frame_every, delay, late_alt=False, hist=250, B=3, seed=3, drop_every=0, check_each=False):
+def _drive(pkg, oracle_mod, NF, n_imu, frame_every, delay, late_alt=False, hist=250, B=3, seed=3, drop_every=0, check_each=False, replace=False, Qxf=0.0):
     """IMU at 250 Hz; a camera frame every `frame_every` samples stamped `delay` seconds in the past (so it lands inside an
     earlier IMU interval and forces a rewind); ACC every sample; optionally an ALT measurement that arrives two IMU samples
     late.  Both filters receive exactly the same calls, in the order vi_ekf_test / the ROS wrapper issue them."""
     rng = np.random.default_rng(seed)
     cfg = abi.default_config()
     cfg.use_keyframe_reset = 0
+    cfg.Qx_feat[:] = [Qxf, Qxf, 0.1 * Qxf]
+    next_new = [NF]
     f = oracle_mod.OracleVIEKF(cfg, NF, hist=hist)
     bk = pkg.BatchVIEKF(cfg, B=B, N=NF)
     bk.enable_queue(hist, 200)
@@ -56,12 +56,16 @@ def _drive(pkg, oracle_mod, NF, n_imu, frame_every, delay, late_alt=False, hist=
                 bk.keep_only_features(keep)
                 for d in [i for i in pix if i not in keep]:
                     del pix[d]
+                if replace:  # the tracker found a replacement: a new id in this frame (the filter numbers it next_feature_id_)
+                    pix[next_new[0]] = np.array([100.0 + 11.0 * (next_new[0] % 40), 90.0 + 7.0 * (next_new[0] % 30)])
+                    next_new[0] += 1
             for i in list(pix):
                 pix[i] = pix[i] + 0.3 * rng.standard_normal(2)
                 r_o = f.add_measurement(tc, pix[i], abi.FEAT, feat_R, True, i, 4.0 + 0.1 * i)
                 r_g = bk.add_measurement(tc, pix[i], abi.FEAT, feat_R, True, i, 4.0 + 0.1 * i)
                 assert r_o == r_g, f"step {k} feature {i}: add_measurement {r_g} vs oracle {r_o}"
-                assert r_g == (abi.MEAS_NEW_FEATURE if k == 0 else abi.MEAS_SUCCESS)
+                if not replace:
+                    assert r_g == (abi.MEAS_NEW_FEATURE if k == 0 else abi.MEAS_SUCCESS)
         if check_each:
             _check(f, bk, f"step {k} before handle_measurements")
         gated_o = f.handle_measurements()
@@ -113,6 +117,17 @@ def test_queue_feature_drops(pkg, oracle_mod):
     f, bk, applied = _drive(pkg, oracle_mod, NF=7, n_imu=160, frame_every=8, delay=0.0302, drop_every=3)
     assert f.get_len_features() < 7
     _check(f, bk, "drops")
+
+
+@pytest.mark.parametrize("Qxf", [0.0, 1e-4])
+def test_queue_new_features_behind_a_rewind(pkg, oracle_mod, Qxf):
+    """A replacement feature arrives in a delayed frame: init_feature writes the current slot only (vi_ekf_feat.cpp:33-41), the
+    next handle_measurements rewinds behind it, and the filter carries on with whatever the older slot held for that index --
+    stale x, and for P the dead-slot block the reference keeps (P0_feat from init() plus Qx_feat per propagate, zeros after a
+    clear_feature).  The engine maintains those dead rows in queue mode, so even this corner follows the reference."""
+    f, bk, applied = _drive(pkg, oracle_mod, NF=5, n_imu=160, frame_every=8, delay=0.0302, drop_every=3, replace=True, Qxf=Qxf)
+    assert max(f.tracked_features()) >= 5
+    _check(f, bk, "new features behind a rewind")
 
 
 def test_queue_reset_and_errors(pkg):

@@ -125,6 +125,8 @@ static void fill_params(viekf_batch* h) {
 
 extern "C" {
 
+static int queue_reset_dead(viekf_batch* h);
+
 const char* viekf_last_error(void) { return g_err.c_str(); }
 
 void viekf_config_default(viekf_config* c) {
@@ -256,6 +258,8 @@ int viekf_batch_reset(viekf_batch* h) {
     q->z.clear();
   }
   CK(vk::launch_reset(h->kp, h->stream));
+  if (h->q)
+    if (int rc = queue_reset_dead(h)) return rc;
   CK(cudaStreamSynchronize(h->stream));
   return VIEKF_OK;
 }
@@ -445,6 +449,25 @@ static viekf_event blank_event(int kind) {
   return e;
 }
 
+// clear_feature / keep_only_features; in queue mode a removal also zeroes the dead region of the current slot, as
+// vi_ekf_feat.cpp:68-71 does
+static int queue_zero_dead(viekf_batch* h, int len);
+static int queue_len(viekf_batch* h, int* len);
+static int run_removal_event(viekf_batch* h, const viekf_event& e) {
+  int before = 0, after = 0;
+  if (h->q)
+    if (int rc = queue_len(h, &before)) return rc;
+  if (int rc = run_single_event(h, e, nullptr, 0, 1, nullptr)) return rc;
+  if (h->q) {
+    if (int rc = queue_len(h, &after)) return rc;
+    if (after < before) {
+      if (int rc = queue_zero_dead(h, after)) return rc;
+      CK(cudaStreamSynchronize(h->stream));
+    }
+  }
+  return VIEKF_OK;
+}
+
 int viekf_batch_propagate(viekf_batch* h, const double* u, int32_t broadcast, double t) {
   if (!h || !u) return fail(VIEKF_ERR_ARG, "bad argument");
   viekf_event e = blank_event(VIEKF_EV_PROP);
@@ -479,7 +502,7 @@ int viekf_batch_clear_feature(viekf_batch* h, int32_t id) {
   if (!h) return fail(VIEKF_ERR_ARG, "null handle");
   viekf_event e = blank_event(VIEKF_EV_CLEAR);
   e.id = id;
-  return run_single_event(h, e, nullptr, 0, 1, nullptr);
+  return run_removal_event(h, e);
 }
 
 int viekf_batch_keep_only_features(viekf_batch* h, const int32_t* ids, int32_t n) {
@@ -490,7 +513,7 @@ int viekf_batch_keep_only_features(viekf_batch* h, const int32_t* ids, int32_t n
   viekf_event e = blank_event(VIEKF_EV_KEEP);
   e.n_ids = n;
   e.ids_off = 0;
-  return run_single_event(h, e, nullptr, 0, 1, nullptr);
+  return run_removal_event(h, e);
 }
 
 int viekf_batch_keyframe_reset(viekf_batch* h) {
@@ -512,6 +535,56 @@ static void host_rota(const double* q, const double* v, double* o) {
   o[0] = v[0] - q[0] * t[0] + (t[1] * b[2] - t[2] * b[1]);
   o[1] = v[1] - q[0] * t[1] + (t[2] * b[0] - t[0] * b[2]);
   o[2] = v[2] - q[0] * t[2] + (t[0] * b[1] - t[1] * b[0]);
+}
+
+// The reference's P is dense over all NUM_FEATURES slots and init() puts P0_feat on every feature block (vi_ekf.cpp:74-80,
+// 137-143); each propagate then adds Qx_feat to the dead diagonals too (A_d = I, G_d = 0 there, vi_ekf.cpp:304) and
+// clear_feature zeroes the whole dead region (vi_ekf_feat.cpp:68-71).  The kernels never touch the rows behind the live prefix
+// of the packed triangle, so in queue mode -- where a rewind can bring a dead block back to life without an init_feature --
+// these rows are kept as the reference would have them.
+__global__ void queue_dead_diag_kernel(double* P, int64_t ps, const FilterMeta* meta, int64_t B, int N, double a0, double a1, double a2,
+                                       int set) {
+  const int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= B * N) return;
+  const int64_t b = idx / N;
+  const int f = (int)(idx % N);
+  if (f < meta[b].len) return;
+  const double a[3] = {a0, a1, a2};
+  for (int k = 0; k < 3; k++) {
+    const int64_t i = 16 + 3 * f + k;
+    double* d = P + b * ps + i * (i + 1) / 2 + i;
+    *d = set ? a[k] : *d + a[k];
+  }
+}
+
+static int queue_dead_diag(viekf_batch* h, const double* a, int set) {
+  if (h->N == 0) return VIEKF_OK;
+  const int64_t n = h->B * h->N;
+  queue_dead_diag_kernel<<<(unsigned)((n + 255) / 256), 256, 0, h->stream>>>(h->kp.P, h->kp.ps, h->kp.meta, h->B, h->N, a[0], a[1], a[2], set);
+  CK(cudaGetLastError());
+  return VIEKF_OK;
+}
+
+// zero x and packed P behind the live prefix of `len` features in the current slot (vi_ekf_feat.cpp:68-71)
+static int queue_zero_dead(viekf_batch* h, int len) {
+  const int n = 16 + 3 * len, m = 17 + 5 * len;
+  const size_t p0 = (size_t)n * (n + 1) / 2;
+  if ((size_t)h->kp.ps > p0)
+    CK(cudaMemset2DAsync(h->kp.P + p0, sizeof(double) * h->kp.ps, 0, sizeof(double) * (h->kp.ps - p0), h->B, h->stream));
+  if (h->kp.xs > m) CK(cudaMemset2DAsync(h->kp.x + m, sizeof(double) * h->kp.xs, 0, sizeof(double) * (h->kp.xs - m), h->B, h->stream));
+  return VIEKF_OK;
+}
+
+static int queue_reset_dead(viekf_batch* h) {  // after launch_reset: every feature block dead, P0_feat on its diagonal
+  if (int rc = queue_zero_dead(h, 0)) return rc;
+  return queue_dead_diag(h, h->cfg.P0_feat, 1);
+}
+
+static int queue_len(viekf_batch* h, int* len) {
+  std::vector<FilterMeta> m;
+  if (int rc = fetch_meta(h, 0, 1, m)) return rc;
+  *len = m[0].len;
+  return VIEKF_OK;
 }
 
 static void queue_select_slot(viekf_batch* h, int slot) {
@@ -552,6 +625,9 @@ int viekf_batch_queue_enable(viekf_batch* h, int32_t len_state_hist, int32_t len
   h->P_main = h->kp.P;
   h->q = q;
   queue_select_slot(h, 0);
+  if (int rc = queue_zero_dead(h, m[0].len)) return rc;
+  if (int rc = queue_dead_diag(h, h->cfg.P0_feat, 1)) return rc;
+  CK(cudaStreamSynchronize(h->stream));
   return VIEKF_OK;
 }
 
@@ -575,19 +651,22 @@ static int queue_propagate_impl(viekf_batch* h, const double* u, double t, bool 
     advance = !(fabs(dt) < 1e-6) && !(dt < 0);  // vi_ekf.cpp:281-290
   }
   if (advance) {
-    // x_[ip] receives the live entries only, P_[ip] is assigned whole (vi_ekf.cpp:301,304): copy the live prefixes of slot i
-    // to slot ip and propagate in place there; what slot ip held beyond them stays, as in the reference.
+    // x_[ip] receives the live entries only, P_[ip] is assigned whole (vi_ekf.cpp:301,304): copy the live prefix of x and all
+    // of P from slot i to slot ip and propagate in place there; what slot ip held in x beyond the prefix stays, as in the
+    // reference.
     std::vector<FilterMeta> m;
     if (int rc = fetch_meta(h, 0, 1, m)) return rc;
-    const int len = m[0].len, n = 16 + 3 * len;
+    const int len = m[0].len;
     const int ip = (q->i + 1) % q->H;
     const double* sx = h->kp.x;
     const double* sP = h->kp.P;
     queue_select_slot(h, ip);
     CK(cudaMemcpy2DAsync(h->kp.x, sizeof(double) * h->kp.xs, sx, sizeof(double) * h->kp.xs, sizeof(double) * (17 + 5 * len), h->B,
                          cudaMemcpyDeviceToDevice, h->stream));
-    CK(cudaMemcpy2DAsync(h->kp.P, sizeof(double) * h->kp.ps, sP, sizeof(double) * h->kp.ps, sizeof(double) * (n * (n + 1) / 2), h->B,
-                         cudaMemcpyDeviceToDevice, h->stream));
+    CK(cudaMemcpyAsync(h->kp.P, sP, sizeof(double) * h->kp.ps * h->B, cudaMemcpyDeviceToDevice, h->stream));  // dead rows included
+    const double* qf = h->cfg.Qx_feat;
+    if (qf[0] != 0.0 || qf[1] != 0.0 || qf[2] != 0.0)
+      if (int rc = queue_dead_diag(h, qf, 0)) return rc;
     q->t[ip] = t;
   }
   return run_single_event(h, e, u, 6, 1, nullptr);
