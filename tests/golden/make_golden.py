@@ -55,7 +55,23 @@ def make(name):
     print(name, "events", len(ev), "len", ref["len"].tolist(), "results", np.bincount(ref["results"][0], minlength=6)[:5].tolist())
 
 
+def make_queue():
+    """Streaming call pattern of BASELINE configs[0] (tests/queue_calls.py) through the oracle's rewind/replay queue."""
+    from tests import queue_calls
+    NF = 12
+    cfg = abi.default_config()
+    calls = queue_calls.config0_calls(pkg, cfg, NF)
+    f = oracle.OracleVIEKF(cfg, NF)
+    adds, gated, _ = queue_calls.replay(calls, f, abi, engine=False)
+    os.makedirs(os.path.join(HERE, "queue"), exist_ok=True)
+    np.savez_compressed(os.path.join(HERE, "queue", "config0_n12.npz"), cfg=np.frombuffer(bytes(cfg), dtype=np.uint8), NF=NF, calls=calls,
+                        adds=np.asarray(adds, dtype=np.int32), gated_n=np.asarray([len(g_) for g_ in gated], dtype=np.int32),
+                        gated=np.asarray([i for g_ in gated for i in g_], dtype=np.int32), x=f.get_state(), P=f.get_covariance(),
+                        len=f.get_len_features(), ids=np.asarray(f.tracked_features(), dtype=np.int32), t=f.time())
+    print("queue/config0_n12 calls", len(calls), "adds", np.bincount(adds, minlength=5).tolist(), "gated", sum(len(g_) for g_ in gated))
+
+
 if __name__ == "__main__":
     oracle.build()
-    for n in (sys.argv[1:] or CASES):
-        make(n)
+    for n in (sys.argv[1:] or list(CASES) + ["queue"]):
+        make_queue() if n == "queue" else make(n)

@@ -130,6 +130,23 @@ def test_queue_new_features_behind_a_rewind(pkg, oracle_mod, Qxf):
     _check(f, bk, "new features behind a rewind")
 
 
+def test_config0_vi_ekf_test_call_pattern(pkg, oracle_mod):
+    """BASELINE configs[0]: the call sequence of the reference's test/vi_ekf_test.cpp:24-33,58 over the restated multirotor_sim
+    stream (tests/queue_calls.py), N = 12 = the reference's release NUM_FEATURES: oracle vs engine, call for call."""
+    from tests import queue_calls
+    NF, B = 12, 2
+    cfg = abi.default_config()
+    calls = queue_calls.config0_calls(pkg, cfg, NF)
+    f = oracle_mod.OracleVIEKF(cfg, NF)
+    bk = pkg.BatchVIEKF(cfg, B=B, N=NF)
+    bk.enable_queue(250, 200)
+    adds_o, gated_o, _ = queue_calls.replay(calls, f, abi, engine=False)
+    adds_g, gated_g, n_upd = queue_calls.replay(calls, bk, abi, engine=True)
+    assert adds_g == adds_o and gated_g == gated_o
+    assert adds_g.count(abi.MEAS_NEW_FEATURE) >= NF and n_upd > 100 and f.get_len_features() == NF
+    _check(f, bk, "configs[0] call pattern")
+
+
 def test_queue_reset_and_errors(pkg):
     cfg = abi.default_config()
     bk = pkg.BatchVIEKF(cfg, B=2, N=2)
