@@ -37,6 +37,16 @@ BIAS = [0.5, 0.5, 0.5, 0.05, 0.05, 0.05]  # sim_params.yaml:150-155 accel_init_s
 
 
 T0 = time.time()
+# The contract is ONE JSON line on stdout.  Libraries write there too (NCCL prints its version banner to fd 1 at init), so the
+# process's fd 1 is pointed at stderr for the whole run and the JSON line goes to a private duplicate of the original stdout.
+JSON_OUT = sys.stdout
+
+
+def isolate_stdout():
+    global JSON_OUT
+    sys.stdout.flush()
+    JSON_OUT = os.fdopen(os.dup(1), "w")
+    os.dup2(2, 1)
 
 
 def log(msg):
@@ -148,7 +158,7 @@ def run_reference(args, rank, world):
         "e2e": {"value": val, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
-    print(json.dumps(line), flush=True)
+    print(json.dumps(line), file=JSON_OUT, flush=True)
 
 
 def kernel_name(n):
@@ -341,7 +351,7 @@ def emit(args, pkg, world, K, W, B, ev, idp, info, slices, cfg, ms_total, ms_e2e
         rate, secs = cpu_leg(pkg, cfg, ev, idp, slices, 2, inst, threads)
         line["cpu_baseline"] = {"value": rate, "unit": UNIT, "cores": threads, "kind": "port",
                                 "sample": f"{inst} instances x {2 * IMU_PER_STEP} IMU samples (first two slices of the same tape), {secs:.1f} s"}
-    print(json.dumps(line), flush=True)
+    print(json.dumps(line), file=JSON_OUT, flush=True)
 
 
 def main():
@@ -354,6 +364,7 @@ def main():
     ap.add_argument("--features", type=int, default=N_FEAT, help="features per filter (default 25: BASELINE configs[3]; 35 = configs[4])")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     args = ap.parse_args()
+    isolate_stdout()
     globals().update(N_FEAT=args.features, B_PER_GPU=args.filters, METRIC=METRIC.replace("25 features", f"{args.features} features"))
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))

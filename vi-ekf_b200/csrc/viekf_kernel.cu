@@ -274,16 +274,20 @@ cudaError_t launch_unpack_cov(const KParams& p, int64_t first, int64_t count, do
 // ------------------------------------------------------------------------------------------------------------------
 // FP64 FMA throughput probe (roofline denominator of the compute-bound kernels)
 // ------------------------------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(256) dfma_probe_kernel(double* out, int iters, double a, double b) {
-  double r0 = threadIdx.x, r1 = r0 + 1, r2 = r0 + 2, r3 = r0 + 3, r4 = r0 + 4, r5 = r0 + 5, r6 = r0 + 6, r7 = r0 + 7;
+// 16 independent chains per thread, 2 CTAs x 512 threads per SM: measured 37.06 TFLOP/s on B200 = 99.6 % of 148 SMs x 64 DFMA/clk x
+// 1.965 GHz (tools/microbench/dmma_peak.cu, profiles/r1_dmma_vs_dfma_microbench.txt); fewer chains / more warps measure ~8 % low
+__global__ void __launch_bounds__(512) dfma_probe_kernel(double* out, int iters, double a, double b) {
+  double r[16];
+#pragma unroll
+  for (int u = 0; u < 16; u++) r[u] = threadIdx.x + u;
   for (int i = 0; i < iters; i++) {
 #pragma unroll
-    for (int u = 0; u < 8; u++) {
-      r0 = fma(r0, a, b); r1 = fma(r1, a, b); r2 = fma(r2, a, b); r3 = fma(r3, a, b);
-      r4 = fma(r4, a, b); r5 = fma(r5, a, b); r6 = fma(r6, a, b); r7 = fma(r7, a, b);
-    }
+    for (int u = 0; u < 16; u++) r[u] = fma(r[u], a, b);
   }
-  out[(size_t)blockIdx.x * blockDim.x + threadIdx.x] = ((r0 + r1) + (r2 + r3)) + ((r4 + r5) + (r6 + r7));
+  double s = 0;
+#pragma unroll
+  for (int u = 0; u < 16; u++) s += r[u];
+  out[(size_t)blockIdx.x * blockDim.x + threadIdx.x] = s;
 }
 cudaError_t fp64_probe(int device, double* tflops) {
   cudaError_t e = cudaSetDevice(device);
@@ -291,7 +295,7 @@ cudaError_t fp64_probe(int device, double* tflops) {
   cudaDeviceProp prop;
   e = cudaGetDeviceProperties(&prop, device);
   if (e != cudaSuccess) return e;
-  const int blocks = prop.multiProcessorCount * 8, threads = 256, iters = 4096;
+  const int blocks = prop.multiProcessorCount * 2, threads = 512, iters = 32768;
   double* d = nullptr;
   e = cudaMalloc(&d, sizeof(double) * blocks * threads);
   if (e != cudaSuccess) return e;
@@ -307,7 +311,7 @@ cudaError_t fp64_probe(int device, double* tflops) {
     if (e != cudaSuccess) break;
     float ms = 0;
     cudaEventElapsedTime(&ms, e0, e1);
-    const double fl = 2.0 * 64.0 * (double)iters * blocks * threads;
+    const double fl = 2.0 * 16.0 * (double)iters * blocks * threads;
     const double tf = fl / (ms * 1e-3) / 1e12;
     if (rep > 0 && tf > best) best = tf;
   }
