@@ -272,6 +272,8 @@ def run_gpu(args, rank, world, local_rank):
     ms_total, ms_e2e = float(t[0]), float(t[1])
     stats = bk.stats(nb)
     if rank == 0:
+        # the roofline denominator: the better of the probe before the run (cold clocks) and after it (boost clocks held)
+        fp64_peak = max(fp64_peak, pkg.batch.fp64_peak_tflops(local_rank))
         emit(args, pkg, world, K, W, B, ev, idp, info, slices, cfg, ms_total, ms_e2e, per_launch_ms, launches, clocks, fp64_peak, ctr0, ctr1, stats,
              h2d // K, d2h // K, nccl_ms)
     bk.free_tape(dtape)
