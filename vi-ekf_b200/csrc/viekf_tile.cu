@@ -1040,6 +1040,7 @@ __global__ void __launch_bounds__(32 * (TW + 1) * FPC, (32 * (TW + 1) * FPC <= 1
   double* evb = base + L.evb;
   constexpr int EVW = (int)(sizeof(viekf_event) / sizeof(double));
   static_assert(sizeof(viekf_event) % sizeof(double) == 0 && EVW <= 32, "viekf_event must fit one warp of doubles");
+  constexpr int EVT0 = (G >= 96) ? 64 : 32;  // first thread of the warp that stages the next event record (warp 2; the base warp when TW = 1)
   const int nmaxp = 16 + 6 * L.TR;
   for (int i = c.tid; i < nmaxp; i += G) c.lam[i] = (i < 16) ? p.lam[i] : p.lamf[(i - 16) % 3];
   for (int i = c.tid; i < 2 * L.TR; i += G) c.fixk[i] = 0;
@@ -1080,7 +1081,7 @@ __global__ void __launch_bounds__(32 * (TW + 1) * FPC, (32 * (TW + 1) * FPC <= 1
       tile_load(c, gP, Pt, len0, false);
     }
     if (p.ev_count > 0 && c.tid < 8) resolve_values(p, p.ev_first, b, ginst, c.tid, c.zvr);
-    if (p.ev_count > 0 && c.tid >= 64 && c.tid < 64 + EVW) evb[c.tid - 64] = ((const double*)(p.ev + p.ev_first))[c.tid - 64];
+    if (p.ev_count > 0 && c.tid >= EVT0 && c.tid < EVT0 + EVW) evb[c.tid - EVT0] = ((const double*)(p.ev + p.ev_first))[c.tid - EVT0];
     PHS(c, 0)
     // ---- run the tape slice ----
     for (int64_t e = p.ev_first; e < p.ev_first + p.ev_count; e++) {
@@ -1089,8 +1090,8 @@ __global__ void __launch_bounds__(32 * (TW + 1) * FPC, (32 * (TW + 1) * FPC <= 1
       const viekf_event& E = *(const viekf_event*)(evb + 32 * (int)((e - p.ev_first) & 1));
       tile_apply_fix(c, p, Pt);  // depth corrections recorded by the previous event
       double ev_next = 0.0;
-      const bool stage = (e + 1 < p.ev_first + p.ev_count) && c.tid >= 64 && c.tid < 64 + EVW;
-      if (stage) ev_next = __ldg((const double*)(p.ev + e + 1) + (c.tid - 64));
+      const bool stage = (e + 1 < p.ev_first + p.ev_count) && c.tid >= EVT0 && c.tid < EVT0 + EVW;
+      if (stage) ev_next = __ldg((const double*)(p.ev + e + 1) + (c.tid - EVT0));
       const int kind = E.kind;
       c.zv = c.zvr + 8 * (int)((e - p.ev_first) & 7);
       c.next_e = (((e - p.ev_first) & 3) == 0 && e + 1 < p.ev_first + p.ev_count) ? e + 1 : -1;
@@ -1130,7 +1131,7 @@ __global__ void __launch_bounds__(32 * (TW + 1) * FPC, (32 * (TW + 1) * FPC <= 1
       }
       if (!c.resolved) resolve_next(c, p, 32);  // the handler returned before its deferred slot (uniform)
       }
-      if (stage) evb[32 * (int)((e + 1 - p.ev_first) & 1) + (c.tid - 64)] = ev_next;
+      if (stage) evb[32 * (int)((e + 1 - p.ev_first) & 1) + (c.tid - EVT0)] = ev_next;
       PH(c, 16 + kind)
       // the filters of a CTA re-align every LOCKSTEP events (all start the next event together); in between only the group
       // synchronises, so a filter that finishes an event early (gated update, fewer live features) is not held back each time
@@ -1186,8 +1187,15 @@ extern "C" int viekf_debug_phase_clocks(unsigned long long* clk, unsigned long l
 }
 #endif
 
-// 91 tiles (N <= 26) fit three tile warps, 171 tiles (N <= 36) six
-int tile_warps_for(int N) { return (N >= 7 && N <= 26) ? 3 : ((N >= 27 && N <= 36) ? 6 : 0); }
+// 28 tiles (N <= 14) fit one tile warp, 91 tiles (N <= 26) three, 171 tiles (N <= 36) six.  VIEKF_TILE_TW1=0 keeps N <= 14 on three
+// tile warps (A/B switch for the one-warp mapping).
+int tile_warps_for(int N) {
+  if (N >= 7 && N <= 14) {
+    const char* s = getenv("VIEKF_TILE_TW1");
+    return (s && atoi(s) == 0) ? 3 : 1;
+  }
+  return (N >= 15 && N <= 26) ? 3 : ((N >= 27 && N <= 36) ? 6 : 0);
+}
 
 template <int TW, int FPC>
 static cudaError_t launch_tile_fpc(const KParams& p, int sm_count, cudaStream_t stream) {
@@ -1222,9 +1230,17 @@ cudaError_t launch_tile(const KParams& p, int sm_count, cudaStream_t stream) {
   // filters per CTA in event lock-step.  TW = 3: 3 (384 threads, 168 registers each: the 72-register tile plus a schedule with
   // loads in flight; 4 x 128 registers spills on the hot path).  TW = 6: 2 (448 threads, 144 registers).  Small batches spread
   // over the SMs first.
-  const int full = (tw == 3) ? 3 : 2;
+  // TW = 1 (N <= 14, config #3 at N = 8): 6 filters of 64 threads per CTA.
+  const int full = (tw == 1) ? 6 : ((tw == 3) ? 3 : 2);
   int fpc = (p.B < full * (int64_t)sm_count) ? 1 : full;
   if (const char* s = getenv("VIEKF_TILE_FPC")) fpc = atoi(s);
+  if (tw == 1) {
+    switch (fpc) {
+      case 1: return launch_tile_fpc<1, 1>(p, sm_count, stream);
+      case 4: return launch_tile_fpc<1, 4>(p, sm_count, stream);
+      default: return launch_tile_fpc<1, 6>(p, sm_count, stream);
+    }
+  }
   if (tw == 3) {
     switch (fpc) {
       case 1: return launch_tile_fpc<3, 1>(p, sm_count, stream);
