@@ -1,6 +1,6 @@
 #!/bin/bash
 # One gpurun call: GPU tests, smoke, both bench arms, ncu launch list and one --set full capture of the tile kernel.
-TAG=${1:-r1_v6}
+TAG=${1:-r1_v7}
 mkdir -p gpurun_out
 python -m pytest tests -m gpu -x -q > gpurun_out/${TAG}_pytest.log 2>&1; echo "pytest rc $?" | tee -a gpurun_out/${TAG}_pytest.log
 python -c "import __graft_entry__ as g; g.smoke(); print('smoke ok')" > gpurun_out/${TAG}_smoke.log 2>&1; echo "smoke rc $?"
