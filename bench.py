@@ -163,7 +163,9 @@ def run_reference(args, rank, world):
 
 def kernel_name(n):
     """The executor launch_tape selects for N features (csrc/viekf_kernel.cu group_size_for, csrc/viekf_tile.cu tile_warps_for)."""
-    if 7 <= n <= 26:
+    if 7 <= n <= 14:
+        return "viekf_tile_kernel<1,6> (register-tile tape executor, one tile warp, 6 filters per CTA)"
+    if 15 <= n <= 26:
         return "viekf_tile_kernel<3,3> (register-tile tape executor, 3 filters per CTA)"
     if 27 <= n <= 36:
         return "viekf_tile_kernel<6,2> (register-tile tape executor, 2 filters per CTA)"
@@ -172,7 +174,9 @@ def kernel_name(n):
 
 def workload_config():
     name = "BASELINE configs[3]" if (N_FEAT, B_PER_GPU) == (25, 262144) else (
-        "BASELINE configs[4] per-GPU shard" if (N_FEAT, B_PER_GPU) == (35, 1048576) else "non-default size of the configs[3] workload")
+        "BASELINE configs[4] per-GPU shard" if (N_FEAT, B_PER_GPU) == (35, 1048576) else (
+        "BASELINE configs[2] (with the configs[3] event mix)" if (N_FEAT, B_PER_GPU) == (8, 65536) else (
+        "BASELINE configs[1] (IMU propagation + ACC-drag / ALT updates)" if (N_FEAT, B_PER_GPU) == (0, 65536) else "non-default size of the configs[3] workload")))
     gb = B_PER_GPU * (17 + 5 * N_FEAT + (16 + 3 * N_FEAT) * (17 + 3 * N_FEAT) // 2) * 8 / 1e9
     return {"workload": f"{name}: {B_PER_GPU} filters x {N_FEAT} features per GPU, 200 Hz IMU / 30 Hz camera, ACC-drag every IMU "
                         f"sample, ALT 25 Hz, keep_only_features churn, Philox per-instance noise; step = {IMU_PER_STEP} IMU samples per filter",

@@ -35,10 +35,19 @@ int group_size_for(int N) {
 // ------------------------------------------------------------------------------------------------------------------
 // the persistent tape executor
 // ------------------------------------------------------------------------------------------------------------------
+#ifndef VIEKF_SMALLG_LOCKSTEP
+#define VIEKF_SMALLG_LOCKSTEP 1
+#endif
+#ifndef VIEKF_SMALLG_CTA
+#define VIEKF_SMALLG_CTA 128  // threads per CTA for G = 32 / 64: VIEKF_SMALLG_CTA / G filters per CTA
+#endif
+#ifndef VIEKF_SMALLG_MINB
+#define VIEKF_SMALLG_MINB 3  // G = 32 / 64 (N <= 6): CTAs of 128 threads per SM the register allocation must admit
+#endif
 template <int G>
-__global__ void __launch_bounds__((G >= 128 ? G : 128), (G == 128 ? 3 : (G == 192 ? 3 : (G == 256 ? 3 : 1)))) viekf_tape_kernel(const __grid_constant__ KParams p) {
+__global__ void __launch_bounds__((G >= 128 ? G : VIEKF_SMALLG_CTA), (G == 128 ? 3 : (G == 192 ? 3 : (G == 256 ? 3 : VIEKF_SMALLG_MINB)))) viekf_tape_kernel(const __grid_constant__ KParams p) {
   extern __shared__ __align__(16) double smem[];
-  constexpr int CTA = (G >= 128 ? G : 128);
+  constexpr int CTA = (G >= 128 ? G : VIEKF_SMALLG_CTA);
   constexpr int GPC = CTA / G;
   const Layout L = make_layout(p.N);
   Ctx<G> c;
@@ -55,7 +64,16 @@ __global__ void __launch_bounds__((G >= 128 ? G : 128), (G == 128 ? 3 : (G == 19
   const int nmax = 16 + 3 * p.N;
   for (int i = c.tid; i < nmax; i += G) c.lam[i] = (i < 16) ? p.lam[i] : p.lamf[(i - 16) % 3];
 
-  for (int64_t b = (int64_t)blockIdx.x * GPC + c.gi; b < p.B; b += (int64_t)gridDim.x * GPC) {
+  // G < 128: the GPC filters of a CTA run the shared tape in event lock-step (one CTA barrier per event), so that the warps of
+  // an SM stay within one event of each other and share the instruction stream (same reasoning as FPC in viekf_tile.cu)
+  constexpr bool LOCK = (GPC > 1) && (VIEKF_SMALLG_LOCKSTEP != 0);
+  for (int64_t b0 = (int64_t)blockIdx.x * GPC; b0 < p.B; b0 += (int64_t)gridDim.x * GPC) {
+    const int64_t b = b0 + c.gi;
+    if (b >= p.B) {  // ragged last round: keep the barrier count of the groups that do have a filter
+      if (LOCK)
+        for (int64_t e = 0; e < p.ev_count; e++) __syncthreads();
+      continue;
+    }
     c.b = b;
     const int64_t ginst = p.inst_off + b;
     FilterMeta& M = p.meta[b];
@@ -119,7 +137,10 @@ __global__ void __launch_bounds__((G >= 128 ? G : 128), (G == 128 ? 3 : (G == 19
         default:
           break;
       }
-      c.sync();
+      if (LOCK)
+        __syncthreads();
+      else
+        c.sync();
       if (p.results && c.tid == 0 && b >= p.res_first && b < p.res_first + p.res_count)
         p.results[(b - p.res_first) * p.n_events + e] = (uint8_t)result;
     }
@@ -148,7 +169,7 @@ __global__ void __launch_bounds__((G >= 128 ? G : 128), (G == 128 ? 3 : (G == 19
 
 template <int G>
 static cudaError_t launch_g(const KParams& p, int sm_count, cudaStream_t stream) {
-  constexpr int CTA = (G >= 128 ? G : 128);
+  constexpr int CTA = (G >= 128 ? G : VIEKF_SMALLG_CTA);
   constexpr int GPC = CTA / G;
   const size_t smem = smem_bytes_per_filter(p.N) * GPC;
   cudaError_t e = cudaFuncSetAttribute(viekf_tape_kernel<G>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
