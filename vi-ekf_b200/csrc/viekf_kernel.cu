@@ -38,6 +38,10 @@ int group_size_for(int N) {
 #ifndef VIEKF_SMALLG_LOCKSTEP
 #define VIEKF_SMALLG_LOCKSTEP 1
 #endif
+#ifndef VIEKF_G64_CTA
+#define VIEKF_G64_CTA 256  // G = 64 (N = 2 ... 6): 4 filters per CTA, 2 CTAs per SM at 128 registers (profiles/r1_v8_smallg_ab.txt)
+#define VIEKF_G64_MINB 2
+#endif
 #ifndef VIEKF_SMALLG_CTA
 #define VIEKF_SMALLG_CTA 128  // threads per CTA for G = 32 / 64: VIEKF_SMALLG_CTA / G filters per CTA
 #endif
@@ -45,9 +49,9 @@ int group_size_for(int N) {
 #define VIEKF_SMALLG_MINB 3  // G = 32 / 64 (N <= 6): CTAs of 128 threads per SM the register allocation must admit
 #endif
 template <int G>
-__global__ void __launch_bounds__((G >= 128 ? G : VIEKF_SMALLG_CTA), (G == 128 ? 3 : (G == 192 ? 3 : (G == 256 ? 3 : VIEKF_SMALLG_MINB)))) viekf_tape_kernel(const __grid_constant__ KParams p) {
+__global__ void __launch_bounds__((G >= 128 ? G : (G == 64 ? VIEKF_G64_CTA : VIEKF_SMALLG_CTA)), (G == 128 ? 3 : (G == 192 ? 3 : (G == 256 ? 3 : (G == 64 ? VIEKF_G64_MINB : VIEKF_SMALLG_MINB))))) viekf_tape_kernel(const __grid_constant__ KParams p) {
   extern __shared__ __align__(16) double smem[];
-  constexpr int CTA = (G >= 128 ? G : VIEKF_SMALLG_CTA);
+  constexpr int CTA = (G >= 128 ? G : (G == 64 ? VIEKF_G64_CTA : VIEKF_SMALLG_CTA));
   constexpr int GPC = CTA / G;
   const Layout L = make_layout(p.N);
   Ctx<G> c;
@@ -169,7 +173,7 @@ __global__ void __launch_bounds__((G >= 128 ? G : VIEKF_SMALLG_CTA), (G == 128 ?
 
 template <int G>
 static cudaError_t launch_g(const KParams& p, int sm_count, cudaStream_t stream) {
-  constexpr int CTA = (G >= 128 ? G : VIEKF_SMALLG_CTA);
+  constexpr int CTA = (G >= 128 ? G : (G == 64 ? VIEKF_G64_CTA : VIEKF_SMALLG_CTA));
   constexpr int GPC = CTA / G;
   const size_t smem = smem_bytes_per_filter(p.N) * GPC;
   cudaError_t e = cudaFuncSetAttribute(viekf_tape_kernel<G>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
