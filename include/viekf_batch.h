@@ -50,7 +50,8 @@ enum {
 /* Per-filter sticky flags (replace the reference's debug-only NAN_CHECK / NEGATIVE_DEPTH exits,
  * include/vi_ekf.h:29-37, src/vi_ekf/vi_ekf_error.cpp). */
 enum {
-  VIEKF_FLAG_NAN_STATE = 1,       /* NaNsInTheHouse() would have fired */
+  VIEKF_FLAG_NAN_STATE = 1,       /* NaNsInTheHouse() (vi_ekf_error.cpp:6-19) fired: NaN in the live x or P; evaluated at every
+                                     STAT event and at the end of every launch (tape slice / per-call entry point) */
   VIEKF_FLAG_DEPTH_NAN_FIXED = 2, /* fix_depth: rho was NaN   (vi_ekf_helper.cpp:137-141) */
   VIEKF_FLAG_DEPTH_NEG_FIXED = 4, /* fix_depth: rho < 0       (vi_ekf_helper.cpp:142-148) */
   VIEKF_FLAG_DEPTH_BIG_FIXED = 8, /* fix_depth: rho > 100     (vi_ekf_helper.cpp:149-154) */
@@ -111,7 +112,9 @@ typedef struct viekf_event {
   int32_t aux;    /* PROP: >= 0 = index of the physical IMU sample; all PROP events of one sample (an interval split by a
                      measurement) then draw the same generated noise; -1 = key the noise by the event index.
                      UPD: 1 = take z[k], k < zdim, from the body-frame IMU input of the filter's last propagate_state
-                     (the drag-accelerometer measurement of src/vi_ekf_ros.cpp:180-184), 0 = use z */
+                     (the drag-accelerometer measurement of src/vi_ekf_ros.cpp:180-184), 0 = use z,
+                     2 = plain update() as replayed by handle_measurements (vi_ekf_meas.cpp:84): no add_measurement bookkeeping,
+                     a FEAT whose id is not tracked is MEAS_INVALID instead of initialising the feature */
   double t;       /* PROP: absolute time of the IMU sample; others: informational */
   double z[8];    /* PROP: u = [acc(3), gyro(3)] in the IMU frame; UPD: z[0..zdim), z[4] = depth (FEAT);
                      INIT: pixel(2), z[4] = depth (NaN = unknown); STAT: true pos(3) vel(3) att(4)=10 -> see truth block */
@@ -138,8 +141,12 @@ typedef struct viekf_tape {
 
 /* Statistics accumulated by STAT events, per bucket (all sums over the filters of this handle):
  * [0] count, [1..16] sum e, [17..32] sum e^2, [33] sum NEES16, [34] sum NEES6 (pos+att),
- * [35] #gated updates so far, [36] #fix_depth interventions so far, [37..39] reserved.
- * e = x_true [-] x_hat on the 16 base error states (reference boxminus, vi_ekf_helper.cpp:100-111). */
+ * [35] #gated updates so far, [36] #fix_depth interventions so far, [37] / [39] number of filters whose NEES16 / NEES6 was
+ * defined (a block that is not positive definite -- exactly zero position covariance right after a keyframe reset -- has no
+ * NEES and is left out of [33] / [34]), [38] number of filters with VIEKF_FLAG_NAN_STATE (excluded from every other column).
+ * e = x_true [-] x_hat on the 16 base error states (reference boxminus, vi_ekf_helper.cpp:100-111); the global truth is first
+ * expressed in the frame of the filter's current keyframe node (inverse of get_global_pose, vi_ekf_kfr.cpp:14-22), which is
+ * the identity until the first keyframe_reset. */
 #define VIEKF_STAT_WIDTH 40
 
 typedef struct viekf_batch viekf_batch; /* opaque */

@@ -56,7 +56,10 @@ void vo_tracked_features(void* h, int* ids) {
   for (size_t i = 0; i < v.size(); i++) ids[i] = v[i];
 }
 double vo_time(void* h) { return ((VIEKF*)h)->time(); }
-unsigned vo_flags(void* h) { return ((VIEKF*)h)->flags; }
+unsigned vo_flags(void* h) {
+  ((VIEKF*)h)->check_nan_state();
+  return ((VIEKF*)h)->flags;
+}
 void vo_counters(void* h, unsigned* c) {
   VIEKF* f = (VIEKF*)h;
   c[0] = f->n_gated;

@@ -145,6 +145,25 @@ int VIEKF::global_to_local_feature_id(int id) const {
   return -1;
 }
 
+// ---- vi_ekf_error.cpp:6-19 -------------------------------------------------------------------------
+// NaNsInTheHouse(): any NaN in the live part of x or in the live block of P.  The reference only evaluates it inside the
+// debug-build NAN_CHECK macro (include/vi_ekf.h:29-33); here it latches the sticky VIEKF_FLAG_NAN_STATE.
+bool VIEKF::nans_in_the_house() const {
+  const int x_max = xZ + len_features_ * 5, dx_max = dxZ + len_features_ * 3;
+  const std::vector<double>& x = x_[i_];
+  const Mat& P = P_[i_];
+  for (int i = 0; i < x_max; i++)
+    if (x[i] != x[i]) return true;
+  for (int j = 0; j < dx_max; j++)
+    for (int i = 0; i < dx_max; i++)
+      if (P(i, j) != P(i, j)) return true;
+  return false;
+}
+bool VIEKF::check_nan_state() {
+  if (nans_in_the_house()) flags |= VIEKF_FLAG_NAN_STATE;
+  return (flags & VIEKF_FLAG_NAN_STATE) != 0;
+}
+
 // ---- vi_ekf_helper.cpp:128-156 ---------------------------------------------------------------------
 void VIEKF::fix_depth() {
   std::vector<double>& x = x_[i_];
@@ -466,6 +485,12 @@ void VIEKF::h(int type, const std::vector<double>& x, double zh[4], Mat& H, int 
 // ---- vi_ekf_meas.cpp:196-278 ------------------------------------------------------------------------------
 int VIEKF::update(Meas& meas) {
   meas.handled = true;
+  // A feature-indexed model whose id is no longer tracked (a queued measurement replayed after keep_only_features dropped
+  // its feature) makes the reference index the state with -1 (UB, vi_ekf_meas.cpp:337,356,371,381).  Defined here, as in
+  // the engine, as MEAS_INVALID with no state change.
+  if ((meas.type == VIEKF_FEAT || meas.type == VIEKF_QZETA || meas.type == VIEKF_DEPTH || meas.type == VIEKF_INV_DEPTH) &&
+      global_to_local_feature_id(meas.id) < 0)
+    return VIEKF_MEAS_INVALID;
   for (int i = 0; i < 4; i++) zhat_[i] = 0;
   H_.zero();
   K_.zero();
@@ -950,6 +975,12 @@ void VIEKF::run_tape(const viekf_event* ev, int64_t n, const int32_t* id_pool, c
         break;
       case VIEKF_EV_STAT: {
         if (!stats || E.id < 0 || E.id >= n_buckets) break;
+        double* s = stats + (size_t)E.id * VIEKF_STAT_WIDTH;
+        // a filter with a NaN in its live state or covariance is flagged, counted, and kept out of every sum
+        if (check_nan_state()) {
+          s[38] += 1.0;
+          break;
+        }
         double xt[17];
         for (int i = 0; i < 8; i++) xt[i] = E.z[i];
         for (int i = 0; i < 9; i++) xt[8 + i] = E.R[i];
@@ -962,13 +993,22 @@ void VIEKF::run_tape(const viekf_event* ev, int64_t n, const int32_t* id_pool, c
             xt[xB_G + i] += bg[i];
           }
         }
+        // The truth is global; after a keyframe reset the filter's position and attitude are relative to the current node
+        // (vi_ekf_kfr.cpp:56-157).  The truth is therefore expressed in the filter's node frame -- the inverse of the
+        // get_global_pose composition (vi_ekf_kfr.cpp:14-22): p_rel = node_q.rotp(p - node_t), q_rel = node_q^-1 * q --
+        // which is the identity map until the first reset.
+        {
+          V3 pr = node_q_.rotp(v3(xt[0] - node_t_[0], xt[1] - node_t_[1], xt[2] - node_t_[2]));
+          Quat qr = node_q_.inverse().otimes(Quat(&xt[xATT]));
+          for (int i = 0; i < 3; i++) xt[i] = pr[i];
+          for (int i = 0; i < 4; i++) xt[xATT + i] = qr.q[i];
+        }
         const std::vector<double>& x = x_[i_];
         double er[16];
         for (int i = 0; i < 6; i++) er[i] = xt[i] - x[i];
         V3 d = Quat(&xt[xATT]).boxminus(Quat(&x[xATT]));
         for (int i = 0; i < 3; i++) er[6 + i] = d[i];
         for (int i = 0; i < 7; i++) er[9 + i] = xt[xB_A + i] - x[xB_A + i];
-        double* s = stats + (size_t)E.id * VIEKF_STAT_WIDTH;
         s[0] += 1.0;
         for (int i = 0; i < 16; i++) {
           s[1 + i] += er[i];
@@ -1001,8 +1041,16 @@ void VIEKF::run_tape(const viekf_event* ev, int64_t n, const int32_t* id_pool, c
         };
         int all[16], pose[6] = {0, 1, 2, 6, 7, 8};
         for (int i = 0; i < 16; i++) all[i] = i;
-        s[33] += nees(all, 16);
-        s[34] += nees(pose, 6);
+        // an undefined (non-finite) NEES is left out of the sum; [37] / [39] count the defined ones
+        const double q16 = nees(all, 16), q6 = nees(pose, 6);
+        if (std::isfinite(q16)) {
+          s[33] += q16;
+          s[37] += 1.0;
+        }
+        if (std::isfinite(q6)) {
+          s[34] += q6;
+          s[39] += 1.0;
+        }
         s[35] += (double)n_gated;
         s[36] += (double)n_fix;
         break;
@@ -1012,6 +1060,7 @@ void VIEKF::run_tape(const viekf_event* ev, int64_t n, const int32_t* id_pool, c
     }
     if (results) results[e] = (uint8_t)res;
   }
+  check_nan_state();  // end of the slice: the engine's executors latch VIEKF_FLAG_NAN_STATE here too
 }
 
 }  // namespace viekf_oracle

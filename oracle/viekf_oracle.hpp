@@ -302,6 +302,8 @@ class VIEKF {
   void keyframe_reset(const std::vector<double>& xm, std::vector<double>& xp, Mat& N);  // vi_ekf_kfr.cpp:6-12
   void fix_depth();                                                  // vi_ekf_helper.cpp:128-156
   int global_to_local_feature_id(int id) const;                      // vi_ekf_helper.cpp:114-125
+  bool nans_in_the_house() const;                                    // vi_ekf_error.cpp:6-19
+  bool check_nan_state();                                            // latches VIEKF_FLAG_NAN_STATE; returns the sticky flag
   void get_global_pose(double t[3], double q[4]) const;              // vi_ekf_kfr.cpp:14-22
   void get_global_cov(double cov[36]) const;                         // vi_ekf_kfr.cpp:24-37
 

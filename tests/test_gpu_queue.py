@@ -166,3 +166,38 @@ def test_queue_reset_and_errors(pkg):
     bk.queue_propagate_state(u, 1.0)
     bk.queue_propagate_state(u, 1.004)
     assert np.array_equal(bk.get_state(), x1)
+
+
+def test_queue_pending_measurement_of_a_dropped_feature(pkg, oracle_mod):
+    """A FEAT measurement is queued, then keep_only_features drops its feature before handle_measurements replays it.  update()
+    never initialises a feature (only add_measurement does, vi_ekf_meas.cpp:140-147): the replayed update is MEAS_INVALID with
+    no state change and next_feature_id_ is not consumed, so later id assignments stay aligned with the oracle."""
+    cfg = abi.default_config()
+    cfg.use_keyframe_reset = 0
+    NF, B = 4, 2
+    f = oracle_mod.OracleVIEKF(cfg, NF)
+    bk = pkg.BatchVIEKF(cfg, B=B, N=NF)
+    bk.enable_queue(250, 200)
+    R = np.diag([0.25, 0.25])
+    u = np.array([0.05, -0.02, -9.80665, 0.01, 0.0, -0.01])
+    pix = {i: np.array([200.0 + 60 * i, 150.0 + 40 * i]) for i in range(3)}
+    for k in range(12):
+        t = 0.004 * (k + 1)
+        f.propagate_state(u, t, True)
+        bk.queue_propagate_state(u, t, True)
+        if k == 0:
+            for i in pix:
+                assert f.add_measurement(t, pix[i], abi.FEAT, R, True, i, 5.0) == bk.add_measurement(t, pix[i], abi.FEAT, R, True, i, 5.0) == abi.MEAS_NEW_FEATURE
+        if k == 6:
+            for i in pix:  # stamped in the past: queued, not yet applied
+                assert f.add_measurement(t - 0.006, pix[i] + 0.2, abi.FEAT, R, True, i) == bk.add_measurement(t - 0.006, pix[i] + 0.2, abi.FEAT, R, True, i) == abi.MEAS_SUCCESS
+            f.keep_only_features([0, 2])
+            bk.keep_only_features([0, 2])
+            go = f.handle_measurements()
+            ty, ids, res = bk.handle_measurements()
+            assert list(ids) == [2, 1, 0] and list(res[:, 0]) == [abi.MEAS_SUCCESS, abi.MEAS_INVALID, abi.MEAS_SUCCESS] and go == []
+        if k == 8:  # the next new feature gets the same internal id on both sides
+            z = np.array([400.0, 300.0])
+            assert f.add_measurement(t, z, abi.FEAT, R, True, 7, 6.0) == bk.add_measurement(t, z, abi.FEAT, R, True, 7, 6.0) == abi.MEAS_NEW_FEATURE
+    _check(f, bk, "pending measurement of a dropped feature")
+    assert f.tracked_features() == [0, 2, 3]

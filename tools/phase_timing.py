@@ -4,10 +4,11 @@ import ctypes, os, sys, io, contextlib, json
 ROOT = os.path.join(os.path.dirname(os.path.abspath(__file__)), "..")
 sys.path.insert(0, ROOT)
 import bench  # noqa: E402
-sys.argv = ["bench.py", "--no-cpu", "--filters", sys.argv[1] if len(sys.argv) > 1 else "32768", "--steps", "3", "--warmup", "3"]
+sys.argv = ["bench.py", "--no-cpu", "--no-secondary", "--filters", sys.argv[1] if len(sys.argv) > 1 else "32768", "--steps", "3", "--warmup", "3"]
 buf = io.StringIO()
-with contextlib.redirect_stdout(buf):
-    bench.main()
+bench.isolate_stdout = lambda: None  # keep the JSON line in this process
+bench.JSON_OUT = buf
+bench.main()
 d = json.loads([l for l in buf.getvalue().splitlines() if l.startswith("{")][-1])
 print("value %.4g ms/launch %s" % (d["value"], d["per_launch_ms"]))
 lib = ctypes.CDLL(bench.g.load_package().abi.lib_path())

@@ -84,7 +84,8 @@ class Tape(C.Structure):
 
 
 def lib_path():
-    return os.path.join(os.path.dirname(os.path.abspath(__file__)), "csrc", "libviekf_b200.so")
+    """In-tree CUDA engine.  VIEKF_LIB (tuning aid) selects another build of the same sources, e.g. the phase-timing one."""
+    return os.environ.get("VIEKF_LIB") or os.path.join(os.path.dirname(os.path.abspath(__file__)), "csrc", "libviekf_b200.so")
 
 
 _lib = None

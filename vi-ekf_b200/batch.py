@@ -115,7 +115,7 @@ class BatchVIEKF:
                                             float(depth), _p(res)))
         return res
 
-    def init_feature(self, pixel, id, depth=-1.0):
+    def init_feature(self, pixel, id, depth=float("nan")):  # NaN = unknown depth, 2 * min_depth (vi_ekf_feat.cpp:24-28)
         pixel = np.ascontiguousarray(pixel, dtype=np.float64)
         bc = 1 if pixel.ndim == 1 else 0
         ok = np.zeros(self.B, dtype=np.uint8)

@@ -182,7 +182,7 @@ int viekf_batch_create(const viekf_config* cfg, int64_t B, int32_t N, int32_t de
     if (v == vk::GROUP_TILE && vk::tile_warps_for(N) > 0) h->group = v;
   }
   const size_t need = (h->group == vk::GROUP_TILE) ? vk::tile_smem_bytes(N)
-                                                   : vk::smem_bytes_per_filter(N) * ((h->group >= 128 ? h->group : 128) / h->group);
+                                                   : vk::smem_bytes_per_filter(N) * vk::smem_filters_per_cta(h->group);
   if (need > (size_t)prop.sharedMemPerBlockOptin) {
     delete h;
     return fail(VIEKF_ERR_UNSUPPORTED, "viekf_batch_create: N too large for the shared-memory resident covariance");
@@ -780,6 +780,7 @@ int viekf_batch_handle_measurements(viekf_batch* h, int32_t* upd_types, int32_t*
     e.active = m.active;
     e.id = m.id;
     e.z[4] = m.depth;
+    e.aux = 2;  // update() without add_measurement's bookkeeping: a feature dropped since it was queued is MEAS_INVALID, not re-initialised
     for (int i = 0; i < m.rdim * m.rdim; i++) e.R[i] = m.R[i];
     uint8_t* out = (upd_results && n_upd < cap) ? upd_results + (size_t)n_upd * h->B : nullptr;
     if (int rc = run_single_event(h, e, m.z, m.zdim, 1, out)) return rc;

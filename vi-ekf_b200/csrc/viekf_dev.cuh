@@ -1051,7 +1051,7 @@ __device__ __forceinline__ int ev_update(Ctx<G>& c, const KParams& p, const viek
   if (feat_type) {
     fi = (E.id >= 0) ? find_feature(c, E.id) : -1;
     if (fi < 0) {
-      if (type == VIEKF_FEAT && E.id >= 0) {
+      if (type == VIEKF_FEAT && E.id >= 0 && E.aux != 2) {  // aux == 2: update() replayed by handle_measurements, which never initialises
         core.init_feature(zv[0], zv[1], E.z[4]);
         return VIEKF_MEAS_NEW_FEATURE;
       }
@@ -1264,10 +1264,36 @@ __device__ __forceinline__ double nees_warp(const double* P, const double* er, i
   return bad ? nan("") : q;
 }
 
+// NaNsInTheHouse (vi_ekf_error.cpp:6-19) for a thread group: every thread passes whether the part of the live x / P it
+// scanned holds a NaN; the sticky VIEKF_FLAG_NAN_STATE is latched and returned (uniformly).
 template <int G>
-__device__ void ev_stat(Ctx<G>& c, const KParams& p, const viekf_event& E, int64_t ginst) {
+__device__ __forceinline__ bool latch_nan_state(const Ctx<G>& c, bool bad) {
+  if (bad) atomicOr((unsigned*)&c.sc[SC_FLAGS], (unsigned)VIEKF_FLAG_NAN_STATE);
+  c.sync();
+  return (c.sc[SC_FLAGS] & VIEKF_FLAG_NAN_STATE) != 0;
+}
+// the scan of the shared-memory executor: live prefix of x and of the packed P
+template <int G>
+__device__ __forceinline__ bool smem_nan_scan(const Ctx<G>& c) {
+  const int len = c.sc[SC_LEN];
+  const int nx = 17 + 5 * len, n = 16 + 3 * len, np = n * (n + 1) / 2;
+  bool bad = false;
+  for (int i = c.tid; i < nx; i += G) bad |= (c.x[i] != c.x[i]);
+  for (int i = c.tid; i < np; i += G) bad |= (c.P[i] != c.P[i]);
+  return bad;
+}
+
+// STAT: `scan()` is the executor's thread-local NaN scan (evaluated only when the event has a valid bucket, as the oracle does).
+template <int G, class Scan>
+__device__ void ev_stat(Ctx<G>& c, const KParams& p, const viekf_event& E, int64_t ginst, Scan scan) {
   if (!p.stats || E.id < 0 || E.id >= p.n_buckets) return;
   c.sync();
+  double* st = p.stats + (size_t)E.id * VIEKF_STAT_WIDTH;
+  // a filter with a NaN in its live state or covariance is flagged, counted in [38], and kept out of every sum
+  if (latch_nan_state(c, scan())) {
+    if (c.tid == 0) atomicAdd(st + 38, 1.0);
+    return;
+  }
   double* er = c.sm + SM_ER;
   double* out = c.sm + SM_HC;  // [2] NEES16, NEES6
   if (c.tid == 0) {
@@ -1286,6 +1312,16 @@ __device__ void ev_stat(Ctx<G>& c, const KParams& p, const viekf_event& E, int64
       xt[10] += ba.x; xt[11] += ba.y; xt[12] += ba.z;
       xt[13] += bg.x; xt[14] += bg.y; xt[15] += bg.z;
     }
+    // the global truth in the frame of the filter's current node: the inverse of get_global_pose (vi_ekf_kfr.cpp:14-22);
+    // the identity map until the first keyframe reset
+    {
+      const FilterMeta& M = p.meta[c.b];
+      const Q4 nq = ldq(M.node_q);
+      const V3 pr = rotp(nq, mk3(xt[0] - M.node_t[0], xt[1] - M.node_t[1], xt[2] - M.node_t[2]));
+      const Q4 qr = otimes(Q4{nq.w, -nq.x, -nq.y, -nq.z}, ldq(xt + 6));
+      xt[0] = pr.x; xt[1] = pr.y; xt[2] = pr.z;
+      stq(xt + 6, qr);
+    }
     const double* x = c.x;
     for (int i = 0; i < 6; i++) er[i] = xt[i] - x[i];
     V3 d = qboxminus(ldq(xt + 6), ldq(x + 6));
@@ -1303,17 +1339,21 @@ __device__ void ev_stat(Ctx<G>& c, const KParams& p, const viekf_event& E, int64
     if ((c.tid & 31) == 0) out[1] = q6;
   }
   c.sync();
-  double* st = p.stats + (size_t)E.id * VIEKF_STAT_WIDTH;
-  for (int k = c.tid; k < 37; k += G) {
+  // an undefined (non-finite) NEES is left out of its sum; [37] / [39] count the defined ones
+  const bool ok16 = isfinite(out[0]), ok6 = isfinite(out[1]);
+  for (int k = c.tid; k < VIEKF_STAT_WIDTH; k += G) {
     double v;
     if (k == 0) v = 1.0;
     else if (k <= 16) v = er[k - 1];
     else if (k <= 32) v = er[k - 17] * er[k - 17];
-    else if (k == 33) v = out[0];
-    else if (k == 34) v = out[1];
+    else if (k == 33) v = ok16 ? out[0] : 0.0;
+    else if (k == 34) v = ok6 ? out[1] : 0.0;
     else if (k == 35) v = (double)c.sc[SC_NGATED];
-    else v = (double)c.sc[SC_NFIX];
-    atomicAdd(st + k, v);
+    else if (k == 36) v = (double)c.sc[SC_NFIX];
+    else if (k == 37) v = ok16 ? 1.0 : 0.0;
+    else if (k == 39) v = ok6 ? 1.0 : 0.0;
+    else continue;
+    if (v != 0.0 || k <= 32) atomicAdd(st + k, v);
   }
   c.sync();
 }

@@ -68,6 +68,8 @@ int group_size_for(int N);
 int tile_warps_for(int N);
 size_t tile_smem_bytes(int N);
 cudaError_t launch_tile(const KParams& p, int sm_count, cudaStream_t stream);
+// filters that share one CTA of the shared-memory executor at this group size
+int smem_filters_per_cta(int group);
 // dynamic shared memory (bytes) one filter needs
 size_t smem_bytes_per_filter(int N);
 // launches the tape executor; grid sized as a multiple of the SM count. Returns cudaError_t.

@@ -48,6 +48,13 @@ int group_size_for(int N) {
 #ifndef VIEKF_SMALLG_MINB
 #define VIEKF_SMALLG_MINB 3  // G = 32 / 64 (N <= 6): CTAs of 128 threads per SM the register allocation must admit
 #endif
+// filters per CTA of the shared-memory executor for a group size: the one constant behind the kernel's launch bounds, its
+// launcher and the create-time shared-memory check
+int smem_filters_per_cta(int group) {
+  if (group >= 128) return 1;
+  return (group == 64 ? VIEKF_G64_CTA : VIEKF_SMALLG_CTA) / group;
+}
+
 template <int G>
 __global__ void __launch_bounds__((G >= 128 ? G : (G == 64 ? VIEKF_G64_CTA : VIEKF_SMALLG_CTA)), (G == 128 ? 3 : (G == 192 ? 3 : (G == 256 ? 3 : (G == 64 ? VIEKF_G64_MINB : VIEKF_SMALLG_MINB))))) viekf_tape_kernel(const __grid_constant__ KParams p) {
   extern __shared__ __align__(16) double smem[];
@@ -136,7 +143,7 @@ __global__ void __launch_bounds__((G >= 128 ? G : (G == 64 ? VIEKF_G64_CTA : VIE
           do_keyframe_reset(c, p);
           break;
         case VIEKF_EV_STAT:
-          ev_stat(c, p, E, ginst);
+          ev_stat(c, p, E, ginst, [&]() { return smem_nan_scan(c); });
           break;
         default:
           break;
@@ -150,6 +157,7 @@ __global__ void __launch_bounds__((G >= 128 ? G : (G == 64 ? VIEKF_G64_CTA : VIE
     }
     // ---- store the filter ----
     c.sync();
+    latch_nan_state(c, smem_nan_scan(c));  // NaNsInTheHouse at the end of the slice
     const int len1 = c.sc[SC_LEN];
     if (c.tid == 0) {
       M.len = len1; M.next_id = c.sc[SC_NEXT]; M.started = c.sc[SC_STARTED]; M.flags = (uint32_t)c.sc[SC_FLAGS];
@@ -320,7 +328,8 @@ cudaError_t fp64_probe(int device, double* tflops) {
   cudaDeviceProp prop;
   e = cudaGetDeviceProperties(&prop, device);
   if (e != cudaSuccess) return e;
-  const int blocks = prop.multiProcessorCount * 2, threads = 512, iters = 32768;
+  // one kernel >= 60 ms (a 5 ms kernel reads ~8 % low: it ends before the clocks have settled): warm-up, then the best of three
+  const int blocks = prop.multiProcessorCount * 2, threads = 512, iters = 32768 * 16;
   double* d = nullptr;
   e = cudaMalloc(&d, sizeof(double) * blocks * threads);
   if (e != cudaSuccess) return e;
@@ -328,7 +337,7 @@ cudaError_t fp64_probe(int device, double* tflops) {
   cudaEventCreate(&e0);
   cudaEventCreate(&e1);
   double best = 0;
-  for (int rep = 0; rep < 5; rep++) {
+  for (int rep = 0; rep < 4; rep++) {
     cudaEventRecord(e0);
     dfma_probe_kernel<<<blocks, threads>>>(d, iters, 0.999999, 1e-9);
     cudaEventRecord(e1);

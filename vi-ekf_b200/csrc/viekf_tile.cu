@@ -984,6 +984,29 @@ __device__ __forceinline__ void tile_keep_only(TCtx<TW>& c, const KParams& p, co
   c.sync();
 }
 
+// NaNsInTheHouse (vi_ekf_error.cpp:6-19), this thread's share: live x, P_bb, live rows of P_fb, and the owner's tile (entries
+// of a padding feature are exact zeros)
+template <int TW>
+__device__ __forceinline__ bool tile_nan_scan(const TCtx<TW>& c, const double (&Pt)[36]) {
+  constexpr int G = 32 * (TW + 1);
+  const int len = c.sc[SC_LEN];
+  bool bad = false;
+  for (int i = c.tid; i < 17 + 5 * len; i += G) bad |= (c.x[i] != c.x[i]);
+  for (int e = c.tid; e < 256; e += G) {
+    const double v = c.Pbb[(e >> 4) * PBS + (e & 15)];
+    bad |= (v != v);
+  }
+  for (int e = c.tid; e < 3 * len * 16; e += G) {
+    const double v = c.Pfb[(e >> 4) * 17 + (e & 15)];
+    bad |= (v != v);
+  }
+  if (c.tile && 2 * c.ti < len) {
+#pragma unroll
+    for (int i = 0; i < 36; i++) bad |= (Pt[i] != Pt[i]);
+  }
+  return bad;
+}
+
 template <int TW>
 struct TileCore {
   TCtx<TW>& c;
@@ -1124,7 +1147,7 @@ __global__ void __launch_bounds__(32 * (TW + 1) * FPC, (32 * (TW + 1) * FPC <= 1
           c.sync();
           tile_pack_base(c);
           c.sync();
-          ev_stat(c, p, E, ginst);
+          ev_stat(c, p, E, ginst, [&]() { return tile_nan_scan(c, Pt); });
           break;
         default:
           break;
@@ -1147,6 +1170,7 @@ __global__ void __launch_bounds__(32 * (TW + 1) * FPC, (32 * (TW + 1) * FPC <= 1
     c.sync();
     if (!active) continue;
     tile_apply_fix(c, p, Pt);
+    latch_nan_state(c, tile_nan_scan(c, Pt));  // NaNsInTheHouse at the end of the slice
     const int len1 = c.sc[SC_LEN];
     if (c.tid == 0) {
       M.len = len1; M.next_id = c.sc[SC_NEXT]; M.started = c.sc[SC_STARTED]; M.flags = (uint32_t)c.sc[SC_FLAGS];
@@ -1233,12 +1257,19 @@ cudaError_t launch_tile(const KParams& p, int sm_count, cudaStream_t stream) {
   // TW = 1 (N <= 14, config #3 at N = 8): 6 filters of 64 threads per CTA.
   const int full = (tw == 1) ? 6 : ((tw == 3) ? 3 : 2);
   int fpc = (p.B < full * (int64_t)sm_count) ? 1 : full;
-  if (const char* s = getenv("VIEKF_TILE_FPC")) fpc = atoi(s);
+  if (const char* s = getenv("VIEKF_TILE_FPC")) fpc = atoi(s);  // test / tuning override; a value without an instantiation is an error
+#ifdef VIEKF_DEV_FAST  // development build: only the configs[3] instantiations (each one costs ~25 s of ptxas)
+  if (tw == 3 && fpc == 1) return launch_tile_fpc<3, 1>(p, sm_count, stream);
+  if (tw == 3 && fpc == 3) return launch_tile_fpc<3, 3>(p, sm_count, stream);
+  return cudaErrorInvalidValue;
+#else
   if (tw == 1) {
     switch (fpc) {
       case 1: return launch_tile_fpc<1, 1>(p, sm_count, stream);
+      case 2: return launch_tile_fpc<1, 2>(p, sm_count, stream);
       case 4: return launch_tile_fpc<1, 4>(p, sm_count, stream);
-      default: return launch_tile_fpc<1, 6>(p, sm_count, stream);
+      case 6: return launch_tile_fpc<1, 6>(p, sm_count, stream);
+      default: return cudaErrorInvalidValue;
     }
   }
   if (tw == 3) {
@@ -1246,10 +1277,16 @@ cudaError_t launch_tile(const KParams& p, int sm_count, cudaStream_t stream) {
       case 1: return launch_tile_fpc<3, 1>(p, sm_count, stream);
       case 2: return launch_tile_fpc<3, 2>(p, sm_count, stream);
       case 3: return launch_tile_fpc<3, 3>(p, sm_count, stream);
-      default: return launch_tile_fpc<3, 4>(p, sm_count, stream);
+      case 4: return launch_tile_fpc<3, 4>(p, sm_count, stream);
+      default: return cudaErrorInvalidValue;
     }
   }
-  return fpc >= 2 ? launch_tile_fpc<6, 2>(p, sm_count, stream) : launch_tile_fpc<6, 1>(p, sm_count, stream);
+  switch (fpc) {
+    case 1: return launch_tile_fpc<6, 1>(p, sm_count, stream);
+    case 2: return launch_tile_fpc<6, 2>(p, sm_count, stream);
+    default: return cudaErrorInvalidValue;
+  }
+#endif
 }
 
 }  // namespace vk

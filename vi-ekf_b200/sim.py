@@ -235,10 +235,16 @@ def build_tape(truth, cfg, N, use_acc=True, use_alt=True, use_feat=True, feat_R=
     def ev_done():
         live.append(len(tracked))
 
+    if use_alt and cfg.use_keyframe_reset:
+        # keyframe_reset re-zeroes the filter's position, z included (vi_ekf_kfr.cpp:63,135), while the altimeter measures the
+        # global altitude (src/vi_ekf_ros.cpp:440,476): the two are inconsistent in the reference itself ("No altimeter for
+        # now", vi_ekf_kfr.cpp:113) -- every ALT update after the first reset would be gated
+        raise ValueError("build_tape: use_alt needs cfg.use_keyframe_reset = 0 (the altimeter measures the global altitude)")
     tb.propagate(truth.imu_u[0], truth.imu_t[0], sigma=imu_sigma, sample=0)  # first call only latches the start time
     ev_done()
     for k in range(1, len(truth.imu_t)):
         tk, uk = truth.imu_t[k], truth.imu_u[k]
+        at_tk = False  # a measurement stamped exactly tk has already propagated the filter there
         while mi < len(meas) and meas[mi][0] <= tk + 1e-9:
             tz, kind, pl = meas[mi]
             mi += 1
@@ -252,9 +258,10 @@ def build_tape(truth, cfg, N, use_acc=True, use_alt=True, use_feat=True, feat_R=
                 pass  # measurement exactly at the IMU time: handled after the closing propagate below
             if kind == 0:
                 vis, xt = pl
-                if abs(tz - tk) <= 1e-9:
+                if abs(tz - tk) <= 1e-9 and not at_tk:
                     tb.propagate(uk, tk, sigma=imu_sigma, sample=k)
                     info["n_prop"] += 1
+                    at_tk = True
                     ev_done()
                 ids = [v[0] for v in vis]
                 dropped = [i for i in tracked if i not in ids]
@@ -276,17 +283,19 @@ def build_tape(truth, cfg, N, use_acc=True, use_alt=True, use_feat=True, feat_R=
                     info["n_feat"] += 1
                     ev_done()
             else:
-                if abs(tz - tk) <= 1e-9:
+                if abs(tz - tk) <= 1e-9 and not at_tk:
                     tb.propagate(uk, tk, sigma=imu_sigma, sample=k)
                     info["n_prop"] += 1
+                    at_tk = True
                     ev_done()
                 tb.update(abi.ALT, [pl], [[alt_R]], sigma=[alt_sigma])
                 info["n_alt"] += 1
                 ev_done()
-        tb.propagate(uk, tk, sigma=imu_sigma, sample=k)  # no-op when a measurement at exactly tk already propagated there
-        info["n_prop"] += 1
+        if not at_tk:  # (a second propagate to the same time would return at once, vi_ekf.cpp:282: not emitted)
+            tb.propagate(uk, tk, sigma=imu_sigma, sample=k)
+            info["n_prop"] += 1
+            ev_done()
         info["n_imu"] += 1
-        ev_done()
         if use_acc:
             # drag accelerometer update with the body-frame xy acceleration of this very IMU sample
             # (src/vi_ekf_ros.cpp:180-184): z is taken from the filter's last propagated input
@@ -320,13 +329,20 @@ def tape_flops(events, live, first=0, count=None):
     totu = 0.0
     nupd = 0
     started = first > 0
+    t_filter = None  # filter time: a propagate with |dt| < 1e-6 returns at once (vi_ekf.cpp:282) and costs nothing
+    for i in range(first - 1, -1, -1):
+        if events[i]["kind"] == abi.EV_PROP:
+            t_filter = float(events[i]["t"])
+            break
     for i in range(first, first + count):
         e = events[i]
         nf = int(live[i])
         if e["kind"] == abi.EV_PROP:
-            if started:
+            t = float(e["t"])
+            if started and (t_filter is None or abs(t - t_filter) >= 1e-6):
                 tot += flops_propagate(nf)
             started = True
+            t_filter = t
         elif e["kind"] == abi.EV_UPD:
             if e["type"] == abi.FEAT and i > 0 and live[i] != live[i - 1]:
                 continue  # initialisation of a new feature, no update
@@ -339,3 +355,25 @@ def hbm_bytes_per_launch(nfeat):
     """x and packed-symmetric P of one filter, read once and written once by a fused launch."""
     n, m = 16 + 3 * nfeat, 17 + 5 * nfeat
     return 2 * (8 * m + 8 * n * (n + 1) // 2) + 48
+
+
+# ---- the benchmark workload (BASELINE.json configs[1..4]): one builder for bench.py and for the parity tests -----------
+BENCH_SEED = 0x5EED
+BENCH_BIAS = [0.5, 0.5, 0.5, 0.05, 0.05, 0.05]  # sim_params.yaml:150-155 accel_init_stdev / gyro_init_stdev
+BENCH_IMU_PER_STEP = 20
+
+
+def bench_workload(N, n_slices, imu_per_step=BENCH_IMU_PER_STEP):
+    """The tape bench.py times: the waypoint flight at 200 Hz IMU / 30 Hz camera with up to N tracked features
+    (keep_only_features churn every frame), a drag-accelerometer update every IMU sample, the altimeter at 25 Hz, per-instance
+    Philox IMU / pixel / altimeter noise and a constant per-instance IMU bias, one STAT event per slice of `imu_per_step`
+    IMU samples.  use_keyframe_reset = 0: the altimeter measures the global altitude, which the reference's keyframe reset
+    is inconsistent with (see build_tape).  Run it with seed = BENCH_SEED, bias_range = BENCH_BIAS, perturb_x0(BENCH_SEED + 1).
+    Returns (cfg, events, id_pool, info, [(first, end)] event range of each slice)."""
+    cfg = abi.default_config()
+    cfg.use_keyframe_reset = 0
+    truth = simulate(cfg, N, n_imu=n_slices * imu_per_step)
+    ev, idp, info = build_tape(truth, cfg, N, stat_every=imu_per_step, depth_known=True)
+    ends = [i + 1 for i in range(len(ev)) if ev[i]["kind"] == abi.EV_STAT]
+    starts = [0] + ends[:-1]
+    return cfg, ev, idp, info, list(zip(starts, ends))
