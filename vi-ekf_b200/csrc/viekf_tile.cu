@@ -1035,7 +1035,13 @@ __global__ void __launch_bounds__(32 * (TW + 1) * FPC, (32 * (TW + 1) * FPC <= 1
   const TLayout L = make_tlayout(p.N);
   TCtx<TW> c;
   c.gi = threadIdx.x / G;
+#ifdef VIEKF_ROLE_ROTATE
+  // warp w of the CTA issues on SM sub-partition w % 4: with G = 128 the base warps of all filters of a CTA would share one
+  // sub-partition (and its 16 FP64 lanes); rotating the roles by the filter index spreads them
+  c.tid = (int)((threadIdx.x % G) + 32 * c.gi) % G;
+#else
   c.tid = threadIdx.x % G;
+#endif
   c.lane = c.tid & 31;
   c.basew = (c.tid >> 5) == TW;
   {
