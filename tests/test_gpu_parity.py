@@ -251,9 +251,9 @@ def test_every_thread_group_mapping(pkg, oracle_mod, group, monkeypatch):
     _compare(bk, ref, tag=f"group={group}")
 
 
-@pytest.mark.parametrize("fpc", [1, 2, 4])
+@pytest.mark.parametrize("fpc", [1, 2, 6])
 def test_tile_executor_filters_per_cta(pkg, oracle_mod, fpc, monkeypatch):
-    """The register-tile executor with 1 / 2 / 4 filters per CTA in event lock-step (B = 6 leaves groups without a filter in
+    """The register-tile executor with 1 / 2 / 6 filters per CTA in event lock-step (B = 6 leaves groups without a filter in
     the last CTA) gives the same decisions and, bit for bit, the same numbers."""
     monkeypatch.setenv("VIEKF_TILE_FPC", str(fpc))
     cfg = _default_cfg()

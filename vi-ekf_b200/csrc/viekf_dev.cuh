@@ -16,7 +16,7 @@ namespace vk {
 struct Layout {
   int x, P, lam, dx, Abd, AbT, T, Ac, Gb, Afd, Gd, Y, upd, small, ids, total;
 };
-__host__ __device__ inline int ev2(int v) { return (v + 1) & ~1; }
+__host__ __device__ constexpr int ev2(int v) { return (v + 1) & ~1; }
 __host__ __device__ inline Layout make_layout(int N) {
   Layout L;
   const int nmax = 16 + 3 * N;
@@ -70,7 +70,7 @@ enum { SM_ZV = 0 /*2 x 8, double buffered*/, SM_HC = 16 /*18*/, SM_RES = 34 /*4*
 // Called by the whole last warp of the group: the zero fill of the continuous blocks is spread over its lanes, the
 // (serial) dynamics and Jacobian entries are written by its last lane.
 template <int G>
-__device__ void base_dynamics(const Ctx<G>& c, const KParams& p, const double* ub) {
+__device__ __forceinline__ void base_dynamics(const Ctx<G>& c, const KParams& p, const double* ub) {
   {
     const int lane = c.tid & 31;
     for (int i = lane; i < 144; i += 32) c.Ac[i] = 0.0;
@@ -137,7 +137,7 @@ __device__ void base_dynamics(const Ctx<G>& c, const KParams& p, const double* u
 
 // continuous feature blocks of feature i: out[27] = A(f,VEL) 3x3 | A(f,B_G) 3x3 | A(f,f) 3x3, plus xdot (vi_ekf_dyn.cpp:96-134)
 template <int G>
-__device__ void feature_dynamics(const Ctx<G>& c, const KParams& p, const double* ub, int i) {
+__device__ __forceinline__ void feature_dynamics(const Ctx<G>& c, const KParams& p, const double* ub, int i) {
   const double* x = c.x;
   V3 vel = ld3(x + 3);
   V3 om = mk3(ub[3] - x[13], ub[4] - x[14], ub[5] - x[15]);
@@ -260,6 +260,177 @@ __device__ __forceinline__ void boxplus_inplace(const Ctx<G>& c, const double* d
   boxplus_impl(c.x, d, s, len, c.tid, G, base_tid);
 }
 
+// Phase B of propagate_state: the discretised rows [A_d | G_d] = [I + A dt + A^2 dt^2/2 | (I + A dt/2 + A^2 dt^2/6) G dt]
+// (vi_ekf.cpp:302-303) from the continuous blocks written by base_dynamics / feature_dynamics; one row per task, tasks
+// first, first + stride, ... < npad; rows n..npad-1 (padding of the register-tile executor) are exact zeros.
+// Every row is evaluated as "load a chunk of inputs into registers, compute, store": inputs and outputs live in the same
+// shared-memory window, so with loads and stores interleaved the compiler has to assume aliasing and serialises one
+// shared-memory round trip per output (this phase cost 8 k cycles per propagate that way).
+template <int G>
+__device__ __forceinline__ void discretise_rows(const Ctx<G>& c, double dt, int n, int npad, int first, int stride) {
+  const double h2 = dt * dt / 2.0, h6 = dt * dt / 6.0, hd2 = dt / 2.0;
+  for (int task = first; task < npad; task += stride) {
+    if (task >= n) {  // padding rows of the register-tile executor: exact zeros
+      double* Ad = c.Afd + (task - 16) * 19;
+#pragma unroll
+      for (int k = 0; k < 19; k++) Ad[k] = 0.0;
+#pragma unroll
+      for (int q = 0; q < 6; q++) c.Gd[task * 6 + q] = 0.0;
+    } else if (task < 16) {
+      const int r = task;
+      double* Ad = c.Abd + r * 16;
+      double* Gd = c.Gd + r * 6;
+      if (r >= 9) {
+#pragma unroll
+        for (int k = 0; k < 16; k++) {
+          const double v = (k == r) ? 1.0 : 0.0;
+          Ad[k] = v;
+          c.AbT[k * 16 + r] = v;
+        }
+#pragma unroll
+        for (int q = 0; q < 6; q++) Gd[q] = 0.0;
+      } else {
+        const double* Ar = c.Ac + r * 16;
+        double ar[16];
+#pragma unroll
+        for (int k = 0; k < 16; k++) ar[k] = Ar[k];
+        double m[9];
+#pragma unroll
+        for (int c0 = 0; c0 < 16; c0 += 4) {  // four columns at a time: 24 operands in registers, four independent chains
+          double av[6][4];
+#pragma unroll
+          for (int k = 0; k < 6; k++)
+#pragma unroll
+            for (int j = 0; j < 4; j++) av[k][j] = c.Ac[(3 + k) * 16 + c0 + j];
+          double o[4];
+#pragma unroll
+          for (int j = 0; j < 4; j++) {
+            const int cc = c0 + j;
+            double aa = 0;
+#pragma unroll
+            for (int k = 3; k < 9; k++) aa += ar[k] * av[k - 3][j];
+            const double id = (cc == r) ? 1.0 : 0.0;
+            o[j] = (id + ar[cc] * dt) + aa * h2;
+            if (cc < 9) m[cc] = (id + ar[cc] * hd2) + aa * h6;
+          }
+#pragma unroll
+          for (int j = 0; j < 4; j++) {
+            Ad[c0 + j] = o[j];
+            c.AbT[(c0 + j) * 16 + r] = o[j];
+          }
+        }
+        double gd[6];
+#pragma unroll
+        for (int q = 0; q < 6; q++) {
+          double s = 0;
+#pragma unroll
+          for (int k = 0; k < 9; k++) s += m[k] * c.Gb[k * 6 + q];
+          gd[q] = s * dt;
+        }
+#pragma unroll
+        for (int q = 0; q < 6; q++) Gd[q] = gd[q];
+      }
+    } else {
+      const int fr = task - 16, i = fr / 3, a = fr - 3 * i;
+      const double* F = c.Y + 27 * i;  // Afv | Afg | Aff (continuous)
+      double* Ad = c.Afd + fr * 19;
+      double* Gd = c.Gd + task * 6;
+      double fv[3], fg[3], ff[3];  // row a of the three continuous blocks
+#pragma unroll
+      for (int k = 0; k < 3; k++) {
+        fv[k] = F[a * 3 + k];
+        fg[k] = F[9 + a * 3 + k];
+        ff[k] = F[18 + a * 3 + k];
+      }
+      double mfb[9];
+#pragma unroll
+      for (int cc = 0; cc < 3; cc++) mfb[cc] = 0.0;
+      // columns VEL (3..5), ATT / B_A (6..11), B_G (12..14), MU (15), in three chunks of the VEL rows of the continuous A
+#pragma unroll
+      for (int c0 = 3; c0 < 16; c0 += 5) {
+        double av[3][5], bk[3][3];
+#pragma unroll
+        for (int k = 0; k < 3; k++)
+#pragma unroll
+          for (int j = 0; j < 5; j++)
+            if (c0 + j < 16) av[k][j] = c.Ac[(3 + k) * 16 + c0 + j];
+        if (c0 == 3) {  // A(f,VEL) block: columns 3..5
+#pragma unroll
+          for (int k = 0; k < 9; k++) bk[k / 3][k % 3] = F[k];
+        } else {        // A(f,B_G) block: columns 12..14
+#pragma unroll
+          for (int k = 0; k < 9; k++) bk[k / 3][k % 3] = F[9 + k];
+        }
+        double o[5];
+#pragma unroll
+        for (int j = 0; j < 5; j++) {
+          const int cc = c0 + j;
+          if (cc < 16) {
+            double aa = 0;
+#pragma unroll
+            for (int k = 0; k < 3; k++) aa += fv[k] * av[k][j];
+            double ac = 0.0;
+            if (cc < 6) {
+#pragma unroll
+              for (int k = 0; k < 3; k++) aa += ff[k] * bk[k][cc - 3];
+              ac = fv[cc - 3];
+            } else if (cc >= 12 && cc < 15) {
+#pragma unroll
+              for (int k = 0; k < 3; k++) aa += ff[k] * bk[k][cc - 12];
+              ac = fg[cc - 12];
+            }
+            o[j] = ac * dt + aa * h2;
+            if (cc < 9) mfb[cc] = ac * hd2 + aa * h6;
+          }
+        }
+        if (c0 == 3) {
+#pragma unroll
+          for (int cc = 0; cc < 3; cc++) Ad[cc] = 0.0;
+        }
+#pragma unroll
+        for (int j = 0; j < 5; j++)
+          if (c0 + j < 16) Ad[c0 + j] = o[j];
+      }
+      double mff[3];
+      {
+        double Bf[9];
+#pragma unroll
+        for (int k = 0; k < 9; k++) Bf[k] = F[18 + k];
+        double o[3];
+#pragma unroll
+        for (int bb = 0; bb < 3; bb++) {
+          double aa = 0;
+#pragma unroll
+          for (int k = 0; k < 3; k++) aa += ff[k] * Bf[k * 3 + bb];
+          const double id = (a == bb) ? 1.0 : 0.0;
+          o[bb] = (id + ff[bb] * dt) + aa * h2;
+          mff[bb] = (id + ff[bb] * hd2) + aa * h6;
+        }
+#pragma unroll
+        for (int bb = 0; bb < 3; bb++) Ad[16 + bb] = o[bb];
+      }
+      {
+        double Bg[9], gd[6];
+#pragma unroll
+        for (int k = 0; k < 9; k++) Bg[k] = F[9 + k];
+#pragma unroll
+        for (int q = 0; q < 6; q++) {
+          double s = 0;
+#pragma unroll
+          for (int k = 3; k < 9; k++) s += mfb[k] * c.Gb[k * 6 + q];
+          if (q >= 3) {
+#pragma unroll
+            for (int k = 0; k < 3; k++) s += mff[k] * Bg[k * 3 + (q - 3)];
+          }
+          gd[q] = s * dt;
+        }
+#pragma unroll
+        for (int q = 0; q < 6; q++) Gd[q] = gd[q];
+      }
+    }
+  }
+}
+
 // Guards of propagate_state, continuous dynamics and the discretised rows [A_d | G_d] (phases A, B).  Returns false
 // (uniformly) when the call does not advance the filter; `npad` >= n rows are written, rows n..npad-1 as zeros.
 template <int G>
@@ -309,81 +480,8 @@ __device__ __forceinline__ bool prop_discretise(Ctx<G>& c, const KParams& p, con
   for (int i = c.tid; i < len; i += G) feature_dynamics(c, p, ub, i);
   c.sync();
   // ---- phase B: discretisation, one row of [A_d | G_d] per task (vi_ekf.cpp:302-303) ----
-  const double h2 = dt * dt / 2.0, h6 = dt * dt / 6.0, hd2 = dt / 2.0;
   const int npad = pad_to_even ? 16 + 3 * ((len + 1) & ~1) : n;
-  for (int task = c.tid; task < npad; task += G) {
-    if (task >= n) {  // padding rows of the register-tile executor: exact zeros
-      double* Ad = c.Afd + (task - 16) * 19;
-      for (int k = 0; k < 19; k++) Ad[k] = 0.0;
-      for (int q = 0; q < 6; q++) c.Gd[task * 6 + q] = 0.0;
-    } else if (task < 16) {
-      const int r = task;
-      double* Ad = c.Abd + r * 16;
-      double* Gd = c.Gd + r * 6;
-      if (r >= 9) {
-        for (int k = 0; k < 16; k++) {
-          Ad[k] = (k == r) ? 1.0 : 0.0;
-          c.AbT[k * 16 + r] = Ad[k];
-        }
-        for (int q = 0; q < 6; q++) Gd[q] = 0.0;
-      } else {
-        const double* Ar = c.Ac + r * 16;
-        double m[9];
-        for (int cc = 0; cc < 16; cc++) {
-          double aa = 0;
-          for (int k = 3; k < 9; k++) aa += Ar[k] * c.Ac[k * 16 + cc];
-          const double id = (cc == r) ? 1.0 : 0.0;
-          Ad[cc] = (id + Ar[cc] * dt) + aa * h2;
-          c.AbT[cc * 16 + r] = Ad[cc];
-          if (cc < 9) m[cc] = (id + Ar[cc] * hd2) + aa * h6;
-        }
-        for (int q = 0; q < 6; q++) {
-          double s = 0;
-          for (int k = 0; k < 9; k++) s += m[k] * c.Gb[k * 6 + q];
-          Gd[q] = s * dt;
-        }
-      }
-    } else {
-      const int fr = task - 16, i = fr / 3, a = fr - 3 * i;
-      const double* F = c.Y + 27 * i;  // Afv | Afg | Aff (continuous)
-      double* Ad = c.Afd + fr * 19;
-      double* Gd = c.Gd + task * 6;
-      double mfb[9];
-      for (int cc = 0; cc < 3; cc++) {
-        Ad[cc] = 0.0;
-        mfb[cc] = 0.0;
-      }
-      for (int cc = 3; cc < 16; cc++) {
-        double aa = 0;
-        for (int k = 0; k < 3; k++) aa += F[a * 3 + k] * c.Ac[(3 + k) * 16 + cc];
-        double ac = 0.0;
-        if (cc < 6) {
-          for (int k = 0; k < 3; k++) aa += F[18 + a * 3 + k] * F[k * 3 + (cc - 3)];
-          ac = F[a * 3 + (cc - 3)];
-        } else if (cc >= 12 && cc < 15) {
-          for (int k = 0; k < 3; k++) aa += F[18 + a * 3 + k] * F[9 + k * 3 + (cc - 12)];
-          ac = F[9 + a * 3 + (cc - 12)];
-        }
-        Ad[cc] = ac * dt + aa * h2;
-        if (cc < 9) mfb[cc] = ac * hd2 + aa * h6;
-      }
-      double mff[3];
-      for (int bb = 0; bb < 3; bb++) {
-        double aa = 0;
-        for (int k = 0; k < 3; k++) aa += F[18 + a * 3 + k] * F[18 + k * 3 + bb];
-        const double id = (a == bb) ? 1.0 : 0.0;
-        Ad[16 + bb] = (id + F[18 + a * 3 + bb] * dt) + aa * h2;
-        mff[bb] = (id + F[18 + a * 3 + bb] * hd2) + aa * h6;
-      }
-      for (int q = 0; q < 6; q++) {
-        double s = 0;
-        for (int k = 3; k < 9; k++) s += mfb[k] * c.Gb[k * 6 + q];
-        if (q >= 3)
-          for (int k = 0; k < 3; k++) s += mff[k] * F[9 + k * 3 + (q - 3)];
-        Gd[q] = s * dt;
-      }
-    }
-  }
+  discretise_rows(c, dt, n, npad, c.tid, G);
   c.sync();
   dt_out = dt;
   len_out = len;
@@ -502,7 +600,7 @@ __device__ void ev_propagate(Ctx<G>& c, const KParams& p, const viekf_event& E) 
 // feature management
 // ------------------------------------------------------------------------------------------------------------------
 template <int G>
-__device__ int find_feature(const Ctx<G>& c, int id) {
+__device__ __forceinline__ int find_feature(const Ctx<G>& c, int id) {
   // global_to_local_feature_id (vi_ekf_helper.cpp:114-125): every warp searches the id list with one ballot per 32 ids
   const int len = c.sc[SC_LEN];
   const int lane = c.tid & 31;
@@ -1023,9 +1121,170 @@ __device__ __forceinline__ void load_h_from_smem(Ctx<G>& c, HReg& H) {
   c.sync();  // cols[8] is re-armed inside the update core
 }
 
+// The three measurement models the Monte-Carlo path lives on (h_feat vi_ekf_meas.cpp:354-367, h_acc drag model :281-296, h_alt
+// :308-315) with h, H and the residual in registers.  Returns false for any other model (generic_model below).
+__device__ __forceinline__ bool fast_model(const double* x, const KParams& p, int type, int rd, const double* zv, int fi, HReg& H) {
+#pragma unroll
+  for (int k = 0; k < 18; k++) H.h[k] = 0.0;
+#pragma unroll
+  for (int k = 0; k < 6; k++) H.col[k] = 0;
+  H.res[0] = H.res[1] = H.res[2] = 0.0;
+  H.m = 0;
+  H.hnan = false;
+  if (type == VIEKF_FEAT && rd == 2) {  // h_feat, vi_ekf_meas.cpp:354-367
+    H.m = 2;
+    H.col[0] = 16 + 3 * fi;
+    H.col[1] = H.col[0] + 1;
+    V3 ze, T0, T1;
+    zeta_T(ldq(x + 17 + 5 * fi), ze, T0, T1);
+    const double iez = 1.0 / ze.z;  // one reciprocal for the four divisions by e_z^T zeta of vi_ekf_meas.cpp:358-366 (1 ulp each)
+    H.res[0] = zv[0] - (p.fl[0] * ze.x * iez + p.cc[0]);
+    H.res[1] = zv[1] - (p.fl[1] * ze.y * iez + p.cc[1]);
+    const double zz[3] = {ze.x, ze.y, ze.z};
+    const double sk[9] = {0, -ze.z, ze.y, ze.z, 0, -ze.x, -ze.y, ze.x, 0};
+    const double Tm[6] = {T0.x, T1.x, T0.y, T1.y, T0.z, T1.z};
+#pragma unroll
+    for (int a = 0; a < 2; a++) {
+      double fb[3], fbs[3];
+#pragma unroll
+      for (int k = 0; k < 3; k++) fb[k] = iez * p.fl[a] * (((k == 2) ? zz[a] : 0.0) * iez - (a == k ? 1.0 : 0.0));
+#pragma unroll
+      for (int k = 0; k < 3; k++) fbs[k] = fb[0] * sk[k] + fb[1] * sk[3 + k] + fb[2] * sk[6 + k];
+#pragma unroll
+      for (int bb = 0; bb < 2; bb++) H.h[a * 6 + bb] = fbs[0] * Tm[bb] + fbs[1] * Tm[2 + bb] + fbs[2] * Tm[4 + bb];
+    }
+    H.hnan = (H.h[0] != H.h[0]) || (H.h[1] != H.h[1]) || (H.h[6] != H.h[6]) || (H.h[7] != H.h[7]);
+    return true;
+  }
+  if (type == VIEKF_ACC && p.use_drag && rd == 2) {  // h_acc drag model, vi_ekf_meas.cpp:281-296
+    const double mu = x[16];
+    H.m = 5;
+    H.col[0] = 3; H.col[1] = 4; H.col[2] = 9; H.col[3] = 10; H.col[4] = 15;
+    H.h[0] = -mu; H.h[2] = 1.0; H.h[4] = -x[3];
+    H.h[6 + 1] = -mu; H.h[6 + 3] = 1.0; H.h[6 + 4] = -x[4];
+    H.res[0] = zv[0] - (-mu * x[3] + x[10]);
+    H.res[1] = zv[1] - (-mu * x[4] + x[11]);
+    H.hnan = (mu != mu) || (x[3] != x[3]) || (x[4] != x[4]);
+    return true;
+  }
+  if (type == VIEKF_ALT && rd == 1) {  // h_alt, vi_ekf_meas.cpp:308-315
+    H.m = 1;
+    H.col[0] = 2;
+    H.h[0] = -1.0;
+    H.res[0] = zv[0] - (-x[2]);
+    H.hnan = false;
+    return true;
+  }
+  return false;
+}
+
+// Every other model (vi_ekf_meas.cpp:281-395), by one thread: H on its (sparse) columns Hc[3][6], residual res[4], cols[0..5] columns,
+// cols[6] = number of live columns, cols[7] = 0, cols[8] = NaN in H.
+__device__ __forceinline__ void generic_model(const double* x, const KParams& p, int type, int zdim, const double* zv, int fi, double* Hc,
+                                              double* res, int* cols) {
+  for (int k = 0; k < 18; k++) Hc[k] = 0.0;
+  double zh[4] = {0, 0, 0, 0};
+  double r4[4] = {0, 0, 0, 0};
+  int m = 0;
+  switch (type) {
+    case VIEKF_ACC:
+      if (p.use_drag) {
+        const double mu = x[16];
+        cols[0] = 3; cols[1] = 4; cols[2] = 9; cols[3] = 10; cols[4] = 15;
+        m = 5;
+        zh[0] = -mu * x[3] + x[10];
+        zh[1] = -mu * x[4] + x[11];
+        Hc[0] = -mu; Hc[2] = 1.0; Hc[4] = -x[3];
+        Hc[6 + 1] = -mu; Hc[6 + 3] = 1.0; Hc[6 + 4] = -x[4];
+      } else {
+        V3 gB = rotp(ldq(x + 6), mk3(0, 0, 9.80665));
+        for (int k = 0; k < 6; k++) cols[k] = 6 + k;
+        m = 6;
+        zh[0] = x[10] - gB.x; zh[1] = x[11] - gB.y; zh[2] = x[12] - gB.z;
+        V3 ng = mk3(-gB.x, -gB.y, -gB.z);
+        const double sk[9] = {0, -ng.z, ng.y, ng.z, 0, -ng.x, -ng.y, ng.x, 0};
+        for (int a = 0; a < 3; a++) {
+          for (int k = 0; k < 3; k++) Hc[a * 6 + k] = sk[a * 3 + k];
+          Hc[a * 6 + 3 + a] = 1.0;
+        }
+      }
+      break;
+    case VIEKF_ALT:
+      cols[0] = 2; m = 1; zh[0] = -x[2]; Hc[0] = -1.0;
+      break;
+    case VIEKF_ATT:
+      for (int k = 0; k < 3; k++) { cols[k] = 6 + k; Hc[k * 6 + k] = 1.0; }
+      m = 3;
+      for (int k = 0; k < 4; k++) zh[k] = x[6 + k];
+      break;
+    case VIEKF_POS:
+      for (int k = 0; k < 3; k++) { cols[k] = k; Hc[k * 6 + k] = 1.0; zh[k] = x[k]; }
+      m = 3;
+      break;
+    case VIEKF_VEL:
+      for (int k = 0; k < 3; k++) { cols[k] = 3 + k; Hc[k * 6 + k] = 1.0; zh[k] = x[3 + k]; }
+      m = 3;
+      break;
+    case VIEKF_QZETA:
+      cols[0] = 16 + 3 * fi; cols[1] = cols[0] + 1; m = 2;
+      Hc[0] = 1.0; Hc[6 + 1] = 1.0;
+      for (int k = 0; k < 4; k++) zh[k] = x[17 + 5 * fi + k];
+      break;
+    case VIEKF_FEAT: {
+      cols[0] = 16 + 3 * fi; cols[1] = cols[0] + 1; m = 2;
+      V3 ze, T0, T1;
+      zeta_T(ldq(x + 17 + 5 * fi), ze, T0, T1);
+      const double ez = ze.z;
+      zh[0] = p.fl[0] * ze.x / ez + p.cc[0];
+      zh[1] = p.fl[1] * ze.y / ez + p.cc[1];
+      // H = (1/ez) F ((zeta e_z^T)/ez - I) [zeta]x T_zeta   (vi_ekf_meas.cpp:366)
+      const double zz[3] = {ze.x, ze.y, ze.z};
+      const double sk[9] = {0, -ze.z, ze.y, ze.z, 0, -ze.x, -ze.y, ze.x, 0};
+      const double Tm[6] = {T0.x, T1.x, T0.y, T1.y, T0.z, T1.z};  // 3x2 row-major
+      for (int a = 0; a < 2; a++) {
+        double fb[3], fbs[3];
+        for (int k = 0; k < 3; k++) fb[k] = (1.0 / ez) * p.fl[a] * (((k == 2) ? zz[a] : 0.0) / ez - (a == k ? 1.0 : 0.0));
+        for (int k = 0; k < 3; k++) fbs[k] = fb[0] * sk[k] + fb[1] * sk[3 + k] + fb[2] * sk[6 + k];
+        for (int bb = 0; bb < 2; bb++) Hc[a * 6 + bb] = fbs[0] * Tm[bb] + fbs[1] * Tm[2 + bb] + fbs[2] * Tm[4 + bb];
+      }
+      break;
+    }
+    case VIEKF_DEPTH: {
+      const double rho = x[17 + 5 * fi + 4];
+      cols[0] = 16 + 3 * fi + 2; m = 1;
+      zh[0] = 1.0 / rho;
+      Hc[0] = -1.0 / (rho * rho);
+      break;
+    }
+    case VIEKF_INV_DEPTH:
+      cols[0] = 16 + 3 * fi + 2; m = 1;
+      zh[0] = x[17 + 5 * fi + 4];
+      Hc[0] = 1.0;
+      break;
+    default:  // PIXEL_VEL: empty stub in the reference (vi_ekf_meas.cpp:388-395): zhat = 0, H = 0
+      m = 0;
+      break;
+  }
+  if (type == VIEKF_QZETA) {
+    qfeat_boxminus(ldq(zv), Q4{zh[0], zh[1], zh[2], zh[3]}, r4);
+  } else if (type == VIEKF_ATT) {
+    V3 d = qboxminus(ldq(zv), Q4{zh[0], zh[1], zh[2], zh[3]});
+    r4[0] = d.x; r4[1] = d.y; r4[2] = d.z;
+  } else {
+    for (int k = 0; k < zdim && k < 4; k++) r4[k] = zv[k] - zh[k];
+  }
+  for (int k = 0; k < 4; k++) res[k] = r4[k];
+  cols[6] = m;
+  cols[7] = 0;  // gate
+  cols[8] = 0;  // nan
+  bool hn = false;
+  for (int k = 0; k < 18; k++) hn |= (Hc[k] != Hc[k]);
+  if (hn) cols[8] = 1;
+}
+
 // update(meas) with add_measurement's bookkeeping in front (vi_ekf_meas.cpp:130-147,196-278). Returns meas_result_t.
-// The covariance-touching steps are delegated to `core` (SmemCore below: P in shared memory; TileCore in viekf_tile.cu:
-// feature covariance in register tiles), which provides run<RD>(E, n, len, H), init_feature(l0, l1, depth), fix_depth(len).
+// The covariance-touching steps are delegated to `core` (SmemCore below: P in shared memory), which provides
+// run<RD>(E, n, len, H), init_feature(l0, l1, depth), fix_depth(len).
 template <int G>
 struct SmemCore {
   Ctx<G>& c;
@@ -1065,164 +1324,13 @@ __device__ __forceinline__ int ev_update(Ctx<G>& c, const KParams& p, const viek
     core.fix_depth(len);
     return VIEKF_MEAS_SUCCESS;
   }
-  // ---- the three models the Monte-Carlo path lives on keep h, H and the residual in registers: every thread evaluates
-  //      them from the same shared state, so no thread-0 section and no broadcast barrier ----
+  // the three models the Monte-Carlo path lives on keep h, H and the residual in registers: every thread evaluates them from
+  // the same shared state, so no thread-0 section and no broadcast barrier; every other model goes through thread 0
   HReg H;
-#pragma unroll
-  for (int k = 0; k < 18; k++) H.h[k] = 0.0;
-#pragma unroll
-  for (int k = 0; k < 6; k++) H.col[k] = 0;
-  H.res[0] = H.res[1] = H.res[2] = 0.0;
-  H.m = 0;
-  H.hnan = false;
-  if (type == VIEKF_FEAT && rd == 2) {  // h_feat, vi_ekf_meas.cpp:354-367
-    const double* x = c.x;
-    H.m = 2;
-    H.col[0] = 16 + 3 * fi;
-    H.col[1] = H.col[0] + 1;
-    V3 ze, T0, T1;
-    zeta_T(ldq(x + 17 + 5 * fi), ze, T0, T1);
-    const double iez = 1.0 / ze.z;  // one reciprocal for the four divisions by e_z^T zeta of vi_ekf_meas.cpp:358-366 (1 ulp each)
-    H.res[0] = zv[0] - (p.fl[0] * ze.x * iez + p.cc[0]);
-    H.res[1] = zv[1] - (p.fl[1] * ze.y * iez + p.cc[1]);
-    const double zz[3] = {ze.x, ze.y, ze.z};
-    const double sk[9] = {0, -ze.z, ze.y, ze.z, 0, -ze.x, -ze.y, ze.x, 0};
-    const double Tm[6] = {T0.x, T1.x, T0.y, T1.y, T0.z, T1.z};
-#pragma unroll
-    for (int a = 0; a < 2; a++) {
-      double fb[3], fbs[3];
-#pragma unroll
-      for (int k = 0; k < 3; k++) fb[k] = iez * p.fl[a] * (((k == 2) ? zz[a] : 0.0) * iez - (a == k ? 1.0 : 0.0));
-#pragma unroll
-      for (int k = 0; k < 3; k++) fbs[k] = fb[0] * sk[k] + fb[1] * sk[3 + k] + fb[2] * sk[6 + k];
-#pragma unroll
-      for (int bb = 0; bb < 2; bb++) H.h[a * 6 + bb] = fbs[0] * Tm[bb] + fbs[1] * Tm[2 + bb] + fbs[2] * Tm[4 + bb];
-    }
-    H.hnan = (H.h[0] != H.h[0]) || (H.h[1] != H.h[1]) || (H.h[6] != H.h[6]) || (H.h[7] != H.h[7]);
-  } else if (type == VIEKF_ACC && p.use_drag && rd == 2) {  // h_acc drag model, vi_ekf_meas.cpp:281-296
-    const double* x = c.x;
-    const double mu = x[16];
-    H.m = 5;
-    H.col[0] = 3; H.col[1] = 4; H.col[2] = 9; H.col[3] = 10; H.col[4] = 15;
-    H.h[0] = -mu; H.h[2] = 1.0; H.h[4] = -x[3];
-    H.h[6 + 1] = -mu; H.h[6 + 3] = 1.0; H.h[6 + 4] = -x[4];
-    H.res[0] = zv[0] - (-mu * x[3] + x[10]);
-    H.res[1] = zv[1] - (-mu * x[4] + x[11]);
-    H.hnan = (mu != mu) || (x[3] != x[3]) || (x[4] != x[4]);
-  } else if (type == VIEKF_ALT && rd == 1) {  // h_alt, vi_ekf_meas.cpp:308-315
-    H.m = 1;
-    H.col[0] = 2;
-    H.h[0] = -1.0;
-    H.res[0] = zv[0] - (-c.x[2]);
-    H.hnan = false;
-  } else {
-  double* Hc = c.sm + SM_HC;   // [3][6]
-  double* res = c.sm + SM_RES; // [4]
-  int* cols = c.sc + SC_COUNT; // [6] + m + gate + nan
-  // ---- every other model: h, H (sparse columns), residual by thread 0 into shared memory ----
-  if (c.tid == 0) {
-    const double* x = c.x;
-    for (int k = 0; k < 18; k++) Hc[k] = 0.0;
-    double zh[4] = {0, 0, 0, 0};
-    double r4[4] = {0, 0, 0, 0};
-    int m = 0;
-    switch (type) {
-      case VIEKF_ACC:
-        if (p.use_drag) {
-          const double mu = x[16];
-          cols[0] = 3; cols[1] = 4; cols[2] = 9; cols[3] = 10; cols[4] = 15;
-          m = 5;
-          zh[0] = -mu * x[3] + x[10];
-          zh[1] = -mu * x[4] + x[11];
-          Hc[0] = -mu; Hc[2] = 1.0; Hc[4] = -x[3];
-          Hc[6 + 1] = -mu; Hc[6 + 3] = 1.0; Hc[6 + 4] = -x[4];
-        } else {
-          V3 gB = rotp(ldq(x + 6), mk3(0, 0, 9.80665));
-          for (int k = 0; k < 6; k++) cols[k] = 6 + k;
-          m = 6;
-          zh[0] = x[10] - gB.x; zh[1] = x[11] - gB.y; zh[2] = x[12] - gB.z;
-          V3 ng = mk3(-gB.x, -gB.y, -gB.z);
-          const double sk[9] = {0, -ng.z, ng.y, ng.z, 0, -ng.x, -ng.y, ng.x, 0};
-          for (int a = 0; a < 3; a++) {
-            for (int k = 0; k < 3; k++) Hc[a * 6 + k] = sk[a * 3 + k];
-            Hc[a * 6 + 3 + a] = 1.0;
-          }
-        }
-        break;
-      case VIEKF_ALT:
-        cols[0] = 2; m = 1; zh[0] = -x[2]; Hc[0] = -1.0;
-        break;
-      case VIEKF_ATT:
-        for (int k = 0; k < 3; k++) { cols[k] = 6 + k; Hc[k * 6 + k] = 1.0; }
-        m = 3;
-        for (int k = 0; k < 4; k++) zh[k] = x[6 + k];
-        break;
-      case VIEKF_POS:
-        for (int k = 0; k < 3; k++) { cols[k] = k; Hc[k * 6 + k] = 1.0; zh[k] = x[k]; }
-        m = 3;
-        break;
-      case VIEKF_VEL:
-        for (int k = 0; k < 3; k++) { cols[k] = 3 + k; Hc[k * 6 + k] = 1.0; zh[k] = x[3 + k]; }
-        m = 3;
-        break;
-      case VIEKF_QZETA:
-        cols[0] = 16 + 3 * fi; cols[1] = cols[0] + 1; m = 2;
-        Hc[0] = 1.0; Hc[6 + 1] = 1.0;
-        for (int k = 0; k < 4; k++) zh[k] = x[17 + 5 * fi + k];
-        break;
-      case VIEKF_FEAT: {
-        cols[0] = 16 + 3 * fi; cols[1] = cols[0] + 1; m = 2;
-        V3 ze, T0, T1;
-        zeta_T(ldq(x + 17 + 5 * fi), ze, T0, T1);
-        const double ez = ze.z;
-        zh[0] = p.fl[0] * ze.x / ez + p.cc[0];
-        zh[1] = p.fl[1] * ze.y / ez + p.cc[1];
-        // H = (1/ez) F ((zeta e_z^T)/ez - I) [zeta]x T_zeta   (vi_ekf_meas.cpp:366)
-        const double zz[3] = {ze.x, ze.y, ze.z};
-        const double sk[9] = {0, -ze.z, ze.y, ze.z, 0, -ze.x, -ze.y, ze.x, 0};
-        const double Tm[6] = {T0.x, T1.x, T0.y, T1.y, T0.z, T1.z};  // 3x2 row-major
-        for (int a = 0; a < 2; a++) {
-          double fb[3], fbs[3];
-          for (int k = 0; k < 3; k++) fb[k] = (1.0 / ez) * p.fl[a] * (((k == 2) ? zz[a] : 0.0) / ez - (a == k ? 1.0 : 0.0));
-          for (int k = 0; k < 3; k++) fbs[k] = fb[0] * sk[k] + fb[1] * sk[3 + k] + fb[2] * sk[6 + k];
-          for (int bb = 0; bb < 2; bb++) Hc[a * 6 + bb] = fbs[0] * Tm[bb] + fbs[1] * Tm[2 + bb] + fbs[2] * Tm[4 + bb];
-        }
-        break;
-      }
-      case VIEKF_DEPTH: {
-        const double rho = x[17 + 5 * fi + 4];
-        cols[0] = 16 + 3 * fi + 2; m = 1;
-        zh[0] = 1.0 / rho;
-        Hc[0] = -1.0 / (rho * rho);
-        break;
-      }
-      case VIEKF_INV_DEPTH:
-        cols[0] = 16 + 3 * fi + 2; m = 1;
-        zh[0] = x[17 + 5 * fi + 4];
-        Hc[0] = 1.0;
-        break;
-      default:  // PIXEL_VEL: empty stub in the reference (vi_ekf_meas.cpp:388-395): zhat = 0, H = 0
-        m = 0;
-        break;
-    }
-    if (type == VIEKF_QZETA) {
-      qfeat_boxminus(ldq(zv), Q4{zh[0], zh[1], zh[2], zh[3]}, r4);
-    } else if (type == VIEKF_ATT) {
-      V3 d = qboxminus(ldq(zv), Q4{zh[0], zh[1], zh[2], zh[3]});
-      r4[0] = d.x; r4[1] = d.y; r4[2] = d.z;
-    } else {
-      for (int k = 0; k < zdim && k < 4; k++) r4[k] = zv[k] - zh[k];
-    }
-    for (int k = 0; k < 4; k++) res[k] = r4[k];
-    cols[6] = m;
-    cols[7] = 0;  // gate
-    cols[8] = 0;  // nan
-    bool hn = false;
-    for (int k = 0; k < 18; k++) hn |= (Hc[k] != Hc[k]);
-    if (hn) cols[8] = 1;
-  }
-  c.sync();
-  load_h_from_smem(c, H);
+  if (!fast_model(c.x, p, type, rd, zv, fi, H)) {
+    if (c.tid == 0) generic_model(c.x, p, type, zdim, zv, fi, c.sm + SM_HC, c.sm + SM_RES, c.sc + SC_COUNT);
+    c.sync();
+    load_h_from_smem(c, H);
   }
   // one call site per residual dimension
   if (rd == 1) return core.template run<1>(E, n, len, H);

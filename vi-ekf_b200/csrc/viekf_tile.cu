@@ -1,17 +1,23 @@
 // viekf_tile.cu -- register-tile tape executor of the VI-EKF batch engine (sm_100a, FP64).
 //
 // Same contract as viekf_kernel.cu (one thread group owns one filter for a whole tape slice; events in order; HBM layout of
-// x / packed P unchanged), different placement of the covariance on chip:
+// x / packed P unchanged), different placement of the covariance on chip and a warp-specialised software pipeline with two
+// roles per filter:
 //
-//   P_ff (feature-feature, the O(N^2) part)  lives in REGISTERS: the lower block-triangle of 2x2-feature tiles (6x6 doubles),
-//                                            one tile per thread of the TW "tile warps"; diagonal tiles keep a mirrored copy
-//   P_bb (16x16, full symmetric), P_fb (3N x 16)  live in shared memory and are owned by the last ("base") warp
+//   P warps (TW of them): the COVARIANCE CHAIN.  P_ff (feature-feature, the O(N^2) part) lives in REGISTERS: the lower
+//     block-triangle of 2x2-feature tiles (6x6 doubles), one tile per thread; diagonal tiles keep a mirrored copy.  P_bb (16x16,
+//     full symmetric) and P_fb (3N x 16) live in shared memory, one row per P thread.  These warps run P H^T, K, the Joseph /
+//     partial rank update (vi_ekf_meas.cpp:254-265) and the structured A_d P A_d^T of propagate_state (vi_ekf.cpp:302-304) as
+//     unrolled FP64 FMA streams on register operands; shared memory only supplies the O(N) row / column vectors.
+//   x warp (one): the STATE CHAIN -- everything that depends on the state x only: boxplus, fix_depth, the next event's
+//     measurement model h / H / residual or the next propagate's continuous dynamics, per-instance noise resolution, and S^-1 with
+//     the Mahalanobis gate.  It runs one event ahead of the P warps: while they apply the rank update of event e, the x warp
+//     applies the state correction of e and prepares the model of e + 1, so the serial scalar work (dependent FP64 chains,
+//     sincos, divisions) is off the critical path.  Its code is one out-of-line function (x_role) with its own register
+//     allocation; the kernel body proper is the P role, whose live ranges are the tile and the operands of the running loop.
 //
-// so the two O(N^2) loops of the filter -- the structured A_d P A_d^T of propagate_state (vi_ekf.cpp:302-304) and the
-// Joseph / partial covariance update (vi_ekf_meas.cpp:254-265) -- run as fully unrolled FP64 FMA streams on register
-// operands; shared memory only supplies the O(N) row / column vectors, mostly as warp broadcasts.  Feature removal
-// (clear_feature / keep_only_features, vi_ekf_feat.cpp:50-142) reshuffles the tiles through the filter's own packed P in
-// global memory (L2 round trip), which is also the load / store path at the ends of a slice.
+// Feature removal (clear_feature / keep_only_features, vi_ekf_feat.cpp:50-142) reshuffles the tiles through the filter's own
+// packed P in global memory (L2 round trip), which is also the load / store path at the ends of a slice.
 //
 // Padding: with `len` live features the tile grid covers lenp = len rounded up to even; every quantity of the padding
 // feature (A_d rows, G_d rows, Y rows, P_fb rows, update vectors, tile entries) is an exact zero, so no per-element guards
@@ -24,10 +30,22 @@ namespace vk {
 constexpr int PBS = 18;  // row stride of P_bb: even (16-byte rows for vector loads), 2-way conflicts at worst for row-per-lane access
 
 struct TLayout {
-  int x, Pbb, Pfb, lam, dx, Abd, AbT, T, Ac, Gb, Afd, Gd, Y, upd, small, ids, smap, evb, fixk, fixv, zvr, total, TR;
+  int x, Pbb, Pfb, lam, dx, Abd, AbT, T, GqT, Ac, Gb, Afd, Gd, Y, upd, small, ids, smap, evb, fixk, fixv, zvr, model, gate, total, TR;
 };
-__host__ __device__ inline TLayout make_tlayout(int N) {
-  TLayout L;
+// prepared model of an event (written by the x warp one event ahead, double buffered by event parity), in doubles
+enum { MD_H = 0 /*18*/, MD_RES = 18 /*3*/, MD_DT = 21, MD_INT = 24 /*int32 part*/, MD_SIZE = 32 };
+enum { MI_COL = 0 /*6*/, MI_M = 6, MI_KIND = 7, MI_FI = 8, MI_HNAN = 9, MI_LEN = 10, MI_PREP = 11 };
+enum { MK_NONE = 0, MK_NAN, MK_INVALID, MK_NEWFEAT, MK_INACTIVE, MK_RUN, MK_PROP_LATCH, MK_PROP_NOP, MK_PROP_BACK, MK_PROP_RUN };
+// S^-1 / gate block of the running update (written by the x warp between the two barriers of the gain computation)
+enum { GD_SI = 0 /*9*/, GD_S = 9 /*9*/, GD_INT = 18, GD_SIZE = 24 };
+enum { GI_GATED = 0, GI_NAN = 1 };
+constexpr int EVSLOTS = 4;  // staged viekf_event records: events e .. e+1 are resident while e runs, e+2 is in flight
+
+// The layout is a function of the capacity CLASS of the executor (14 / 26 / 36 features for 1 / 3 / 6 tile warps), not of the
+// handle's N: every offset is then a compile-time constant, shared-memory accesses use immediate offsets off one base register,
+// and the ~30 per-array pointers need no registers (they were the bulk of the kernel's local-memory traffic).
+__host__ __device__ constexpr TLayout make_tlayout(int N) {
+  TLayout L{};
   L.TR = (N + 1) / 2;
   const int NP = 2 * L.TR;
   const int nmaxp = 16 + 3 * NP;
@@ -40,6 +58,7 @@ __host__ __device__ inline TLayout make_tlayout(int N) {
   L.Abd = o;   o += 256;
   L.AbT = o;   o += 256;
   L.T = o;     o += 16 * 17;             // A_bb P_bb, row stride 17 (conflict-free row-per-lane reads); also the packed P_bb copy
+  L.GqT = o;   o += 96;                  // Qu[q] G_d(cc, q), [q][cc]: the base factor of G_d Qu G_d^T for the P'_fb rows
   L.Ac = o;    o += 144;
   L.Gb = o;    o += 54 + 2;
   L.Afd = o;   o += ev2(3 * NP * 19);
@@ -51,29 +70,38 @@ __host__ __device__ inline TLayout make_tlayout(int N) {
   L.small = o; o += 80;
   L.ids = o;   o += ev2(N + 12);
   L.smap = o;  o += ev2(NP / 2 + 2);
-  L.evb = o;   o += 64;                  // two staged viekf_event records (31 doubles each): the current and the next event
+  L.evb = o;   o += 32 * EVSLOTS;        // staged viekf_event records (31 doubles each)
   L.fixk = o;  o += ev2(NP / 2 + 1);     // pending fix_depth covariance corrections per feature: kind (int32) ...
   L.fixv = o;  o += NP;                  // ... and value
   L.zvr = o;   o += 64;                  // ring of 8 resolved value blocks (8 doubles each): event r reads block r & 7
+  L.model = o; o += 2 * MD_SIZE;
+  L.gate = o;  o += GD_SIZE;
   L.total = ev2(o);
   return L;
 }
 
-size_t tile_smem_bytes(int N) { return (size_t)make_tlayout(N).total * sizeof(double); }
+template <int TW>
+__host__ __device__ constexpr int tile_cap() {
+  return TW == 1 ? 14 : (TW == 3 ? 26 : 36);
+}
+size_t tile_smem_bytes(int N) {
+  const int tw = tile_warps_for(N);
+  return (size_t)make_tlayout(tw == 1 ? 14 : (tw == 3 ? 26 : 36)).total * sizeof(double);
+}
 
-// Optional phase timing (build with -DVIEKF_PHASE_TIMING): thread 0 of every CTA adds the clocks between consecutive marks to
-// g_phase_clk[k]; since the marks sit right after barriers this is the elapsed time of each phase on the CTA's critical path.
+// Optional phase timing (build with -DVIEKF_PHASE_TIMING): lane 0 of every warp adds the clocks between consecutive marks to
+// g_phase_clk[role][k]; since the marks sit right after barriers this is the elapsed time of each phase on that warp.
 #ifdef VIEKF_PHASE_TIMING
-__device__ unsigned long long g_phase_clk[4 * 64];
-__device__ unsigned long long g_phase_cnt[4 * 64];
+__device__ unsigned long long g_phase_clk[8 * 64];
+__device__ unsigned long long g_phase_cnt[8 * 64];
 #define PH_DECL long long ph_last;
 #define PH_INIT(c) (c).ph_last = clock64();
-// slot k: work of the phase (mark before the barrier); slot k + 32: wait at the barrier (mark after it); one row per warp
+// slot k: work of the phase (mark before the barrier); slot k + 32: wait at the barrier (mark after it); one row per warp role
 #define PH(c, k)                                                                                  \
-  if ((threadIdx.x & 31) == 0) {                                                                  \
+  if (((c).tid & 31) == 0) {                                                                      \
     const long long ph_now = clock64();                                                           \
-    atomicAdd(&g_phase_clk[64 * ((threadIdx.x >> 5) & 3) + (k)], (unsigned long long)(ph_now - (c).ph_last)); \
-    atomicAdd(&g_phase_cnt[64 * ((threadIdx.x >> 5) & 3) + (k)], 1ull);                                 \
+    atomicAdd(&g_phase_clk[64 * (((c).tid >> 5) & 7) + (k)], (unsigned long long)(ph_now - (c).ph_last)); \
+    atomicAdd(&g_phase_cnt[64 * (((c).tid >> 5) & 7) + (k)], 1ull);                                 \
     (c).ph_last = ph_now;                                                                         \
   }
 #define PHS(c, k) \
@@ -87,33 +115,20 @@ __device__ unsigned long long g_phase_cnt[4 * 64];
 #define PHS(c, k) (c).sync();
 #endif
 
+// G = 32 (TW + 1) threads per filter: TW P warps, then the x warp
 template <int TW>
 struct TCtx : Ctx<32 * (TW + 1)> {
-  double *Pbb, *Pfb, *fixv;
+  double *Pbb, *Pfb, *GqT, *fixv, *zvr, *model, *gate, *evb;
   int *smap, *fixk;
   int ti, tj;   // tile coordinates in units of 2 features, ti >= tj
   bool tile;    // this thread owns a tile of the (capacity) grid
-  bool basew;   // this thread belongs to the base warp
+  bool xw;      // this thread belongs to the x warp
   int lane;
-  // per-instance values (Philox noise: a ~400-instruction dependent chain per value) are resolved four events at a time --
-  // every fourth event, one warp resolves events e+1..e+4 on 4 x 8 lanes -- by a warp that has slack in that event: the base
-  // warp in propagate phase D2, warp 1 in the rank-update phase; otherwise by warp 1 up front
-  int64_t next_e;    // first event to resolve in this event's slot, -1 = none
   int64_t ginst;
-  double* zvr;       // ring of 8 value blocks
-  bool resolved;
   PH_DECL
+  // barrier among the P warps of the group only (ids 9.. next to the group barriers 1..8)
+  __device__ __forceinline__ void psync() const { asm volatile("bar.sync %0, %1;" ::"r"(this->gi + 9), "r"(32 * TW) : "memory"); }
 };
-
-template <int TW>
-__device__ __forceinline__ void resolve_next(TCtx<TW>& c, const KParams& p, int first_tid) {
-  if (c.next_e >= 0 && c.tid >= first_tid && c.tid < first_tid + 32) {
-    const int l = c.tid - first_tid;
-    const int64_t ev = c.next_e + (l >> 3);
-    if (ev < p.ev_first + p.ev_count) resolve_values(p, ev, c.b, c.ginst, l & 7, c.zvr + 8 * (int)((ev - p.ev_first) & 7));
-  }
-  c.resolved = true;
-}
 
 #define PT(r, c) Pt[(r) * 6 + (c)]
 
@@ -121,15 +136,6 @@ __device__ __forceinline__ void resolve_next(TCtx<TW>& c, const KParams& p, int 
 #define VIEKF_LOCKSTEP 1
 #endif
 constexpr int LOCKSTEP = VIEKF_LOCKSTEP;  // events between CTA-wide barriers (power of two)
-
-
-// Base-warp threads own no tile: their Pt is all zeros for the whole launch.  Re-zeroing it at the end of a base-warp-only
-// section makes the 72 tile registers dead inside that section, so its loops get the full register budget (loads batched
-// ahead of the FMAs instead of one load-use round trip per FMA pair).
-__device__ __forceinline__ void tile_dead(double (&Pt)[36]) {
-#pragma unroll
-  for (int i = 0; i < 36; i++) Pt[i] = 0.0;
-}
 
 template <int TW>
 __device__ __forceinline__ void tile_mirror(const TCtx<TW>& c, double (&Pt)[36]) {
@@ -280,59 +286,275 @@ __device__ __forceinline__ void rows(double (&acc)[W], const double* a, const do
   if (K & 1) fma_row<W>(acc, av, v);
 }
 
-// Base-warp loops live in out-of-line functions: the caller's 72 tile registers are dead there (tile_dead), so these get
-// their own register allocation and a latency-tolerant schedule (loads batched ahead of the FMAs) instead of the
-// pressure-minimising one the 128-register kernel body forces.
-//
-// P'_fb = Y A_bb^T + G_d,f Qu G_d,b^T: one row per lane, 16 independent accumulators, operands as warp broadcasts.
-// GqT[q][cc] = Qu[q] G_d(cc, q) goes to the T buffer (idle since D1).
-static __device__ __noinline__ void base_pfb(const double* Y, const double* AbT, const double* Gd, double* GqT, double* Pfb, const double* Qu, int nfr,
-                                             int lane) {
-  __builtin_assume(__isShared(Y));
-  __builtin_assume(__isShared(AbT));
-  __builtin_assume(__isShared(Gd));
-  __builtin_assume(__isShared(GqT));
-  __builtin_assume(__isShared(Pfb));
-  for (int e = lane; e < 96; e += 32) {
-    const int q = e >> 4, cc = e & 15;
-    GqT[e] = Gd[cc * 6 + q] * Qu[q];
+// ------------------------------------------------------------------------------------------------------------------
+// the x warp: state chain
+// ------------------------------------------------------------------------------------------------------------------
+template <int TW>
+__device__ __forceinline__ void init_tctx(TCtx<TW>& c, double* base) {
+  constexpr TLayout L = make_tlayout(tile_cap<TW>());
+  constexpr int N = tile_cap<TW>();
+  c.x = base + L.x; c.P = base + L.T; c.lam = base + L.lam; c.dx = base + L.dx; c.Abd = base + L.Abd; c.AbT = base + L.AbT; c.T = base + L.T;
+  c.Ac = base + L.Ac; c.Gb = base + L.Gb; c.Afd = base + L.Afd; c.Gd = base + L.Gd; c.Y = base + L.Y; c.upd = base + L.upd;
+  c.Pbb = base + L.Pbb; c.Pfb = base + L.Pfb; c.GqT = base + L.GqT;
+  c.sm = base + L.small;
+  c.ids = (int*)(base + L.ids);
+  c.rm = c.ids + N;
+  c.sc = c.rm + N;
+  c.smap = (int*)(base + L.smap);
+  c.fixk = (int*)(base + L.fixk);
+  c.fixv = base + L.fixv;
+  c.zvr = base + L.zvr;
+  c.model = base + L.model;
+  c.gate = base + L.gate;
+  c.evb = base + L.evb;
+  c.tcur = c.sm + SM_T;
+  c.zv = c.zvr;
+}
+
+// x <- x [+] d s (vi_ekf_helper.cpp:88-98) on the x warp: item i < len is feature i, item len is the base state; one item per lane,
+// all in one pass for len <= 31.  Both kinds of item share the expensive part -- q' = exp(v) (x) q or q (x) exp(v), with sincos,
+// a square root and a division inside exp -- so the base state does not cost a second pass through it.
+static __device__ __noinline__ void xw_boxplus(double* x, const double* d, double s, int len, int lane) {
+  for (int it = lane; it <= len; it += 32) {
+    const bool isb = (it == len);
+    double* xq = isb ? x + 6 : x + 17 + 5 * it;
+    const Q4 q = ldq(xq);
+    V3 dv;
+    if (isb) {
+      for (int k = 0; k < 6; k++) x[k] += d[k] * s;
+      dv = mk3(d[6] * s, d[7] * s, d[8] * s);
+      for (int k = 0; k < 7; k++) x[10 + k] += d[9 + k] * s;
+    } else {
+      const double* df = d + 16 + 3 * it;
+      const double d0 = df[0] * s, d1 = df[1] * s;
+      const V3 T0 = rota(q, mk3(1, 0, 0)), T1 = rota(q, mk3(0, 1, 0));
+      dv = mk3(T0.x * d0 + T1.x * d1, T0.y * d0 + T1.y * d1, T0.z * d0 + T1.z * d1);
+      xq[4] += df[2] * s;
+    }
+    const Q4 e = qexp(dv);
+    const Q4 a = isb ? q : e, b = isb ? e : q;  // base: q (x) exp(v); feature: exp(T_zeta d) (x) q
+    stq(xq, otimes(a, b));
+  }
+}
+
+// per-instance values (Philox noise: a ~400-instruction dependent chain per value) of events rel .. rel+3, 4 x 8 lanes, into the ring
+template <int TW>
+__device__ __forceinline__ void xw_resolve(const TCtx<TW>& c, const KParams& p, int64_t rel) {
+  const int64_t r = rel + (c.lane >> 3);
+  if (r < p.ev_count) resolve_values(p, p.ev_first + r, c.b, c.ginst, c.lane & 7, c.zvr + 8 * (int)(r & 7));
+}
+
+// continuous dynamics and Jacobian blocks of propagate_state (phase A, vi_ekf_dyn.cpp:14-135) on the 32 lanes of the x warp
+template <int TW>
+__device__ __forceinline__ void xw_phase_a(const TCtx<TW>& c, const KParams& p, const double* ub, int len) {
+  base_dynamics(c, p, ub);  // zero fill by the warp, entries by lane 31
+  for (int i = c.lane; i < len; i += 32) feature_dynamics(c, p, ub, i);
+}
+
+// Prepares event `rel` (relative to ev_first) while the covariance warps are still busy with the event before it (kind
+// `cur_kind`, -1 = none): everything that depends on the state x only.
+//   UPD:  add_measurement's bookkeeping (NaN reject, feature lookup, new feature / invalid id, vi_ekf_meas.cpp:130-147), the
+//         measurement model h, H and the residual (vi_ekf_meas.cpp:203-228,281-395)
+//   PROP: the body-frame input, the guards of propagate_state (vi_ekf.cpp:265-290) and the continuous dynamics (phase A)
+// Precondition: x, ids, len, started, time are those event `rel` will see (the x warp itself wrote them, or a group barrier
+// followed the handler that did).
+template <int TW>
+static __device__ __noinline__ void xw_prepare(const KParams& p, double* base, int gi, int lane, int64_t b, int rel, int cur_kind) {
+  constexpr int G = 32 * (TW + 1);
+  TCtx<TW> c;
+  init_tctx(c, base);
+  c.gi = gi;
+  c.tid = G - 32 + lane;
+  c.lane = lane;
+  c.b = b;
+  const viekf_event& E = *(const viekf_event*)(c.evb + 32 * (rel & (EVSLOTS - 1)));
+  double* M = c.model + MD_SIZE * (rel & 1);
+  int* Mi = (int*)(M + MD_INT);
+  const double* zvs = c.zvr + 8 * (rel & 7);
+  const int kind = E.kind;
+  if (kind == VIEKF_EV_PROP) {
+    double ub[6];
+    {
+      Q4 qbu = ldq(p.qbu);
+      V3 a = rota(qbu, mk3(zvs[0], zvs[1], zvs[2])), g = rota(qbu, mk3(zvs[3], zvs[4], zvs[5]));
+      ub[0] = a.x; ub[1] = a.y; ub[2] = a.z; ub[3] = g.x; ub[4] = g.y; ub[5] = g.z;
+    }
+    // the body-frame input of the latest propagate_state call is kept for UPD events with aux == 1 (vi_ekf.cpp:265-267); any
+    // such event before this PROP has already taken its values
+    if (lane < 6) c.sm[SM_UB + lane] = ub[lane];
+    const int started = c.sc[SC_STARTED];
+    const double dt = E.t - *c.tcur;
+    int mk = MK_PROP_RUN;
+    if (!started) mk = MK_PROP_LATCH;
+    else if (fabs(dt) < 1e-6) mk = MK_PROP_NOP;
+    else if (dt < 0) mk = MK_PROP_BACK;
+    const int len = c.sc[SC_LEN];
+    // phase A writes the continuous feature blocks into the Y buffer, which a running propagate still reads: deferred then
+    const bool defer = (cur_kind == VIEKF_EV_PROP);
+    if (mk == MK_PROP_RUN && !defer) xw_phase_a(c, p, ub, len);
+    if (lane == 0) {
+      Mi[MI_KIND] = mk;
+      Mi[MI_LEN] = len;
+      Mi[MI_PREP] = (mk == MK_PROP_RUN && !defer) ? 1 : 0;
+      M[MD_DT] = dt;
+    }
+  } else if (kind == VIEKF_EV_UPD) {
+    const double* zv = (E.aux == 1) ? (c.sm + SM_UB) : zvs;
+    const int type = E.type, zdim = E.zdim, rd = E.rdim;
+    int mk = MK_RUN, fi = -1;
+    bool zn = false;
+    for (int k = 0; k < zdim; k++) zn |= (zv[k] != zv[k]);
+    if (zn) {
+      mk = MK_NAN;
+    } else {
+      const bool feat_type = (type == VIEKF_FEAT || type == VIEKF_QZETA || type == VIEKF_DEPTH || type == VIEKF_INV_DEPTH);
+      if (feat_type) {
+        fi = (E.id >= 0) ? find_feature(c, E.id) : -1;
+        if (fi < 0)  // aux == 2: update() replayed by handle_measurements, which never initialises
+          mk = (type == VIEKF_FEAT && E.id >= 0 && E.aux != 2) ? MK_NEWFEAT : MK_INVALID;
+      }
+      if (mk == MK_RUN && !E.active) mk = MK_INACTIVE;  // logged only: no gate, no correction, but fix_depth still runs
+    }
+    if (mk == MK_RUN) {
+      HReg H;
+      if (fast_model(c.x, p, type, rd, zv, fi, H)) {
+        if (lane == 0) {
+#pragma unroll
+          for (int k = 0; k < 18; k++) M[MD_H + k] = H.h[k];
+#pragma unroll
+          for (int k = 0; k < 3; k++) M[MD_RES + k] = H.res[k];
+#pragma unroll
+          for (int k = 0; k < 6; k++) Mi[MI_COL + k] = H.col[k];
+          Mi[MI_M] = H.m;
+          Mi[MI_HNAN] = H.hnan ? 1 : 0;
+        }
+      } else if (lane == 0) {
+        int cols[9] = {0, 0, 0, 0, 0, 0, 0, 0, 0};
+        double res[4];
+        generic_model(c.x, p, type, zdim, zv, fi, M + MD_H, res, cols);
+        for (int k = 0; k < 3; k++) M[MD_RES + k] = res[k];
+        for (int k = 0; k < 6; k++) Mi[MI_COL + k] = cols[k];
+        Mi[MI_M] = cols[6];
+        Mi[MI_HNAN] = cols[8];
+      }
+    }
+    if (lane == 0) {
+      Mi[MI_KIND] = mk;
+      Mi[MI_FI] = fi;
+      Mi[MI_LEN] = c.sc[SC_LEN];
+    }
   }
   __syncwarp();
-  for (int fr = lane; fr < nfr; fr += 32) {
-    const double* Yr = Y + fr * 17;
-    const double* Gr = Gd + (16 + fr) * 6;
-    double acc[16];
+}
+
+// Pt(r, cc) += sum_k a[r * ars + k * aks] * b[cc * brs + k * bks], k < K: the rank-K correction of a 6x6 tile from two 6xK operand
+// blocks in shared memory.  Software-pipelined by hand like rows<>: the twelve operands of step k+1 are loaded into their own
+// registers before the 36 FMAs of step k are issued (left to itself ptxas keeps ONE operand register and exposes a
+// shared-memory round trip, ~30 clk, per group of six FMAs).
+__device__ __forceinline__ void ld6(double (&v)[6], const double* s, int stride) {
 #pragma unroll
-    for (int q = 0; q < 16; q++) acc[q] = 0.0;
-    rows<16, 16, 1, 16, true>(acc, Yr, AbT);
-    rows<16, 6, 1, 16, true>(acc, Gr, GqT);
-    double* Pr = Pfb + fr * 17;
+  for (int r = 0; r < 6; r++) v[r] = s[r * stride];
+}
+__device__ __forceinline__ void fma66(double (&Pt)[36], const double (&a)[6], const double (&b)[6]) {
 #pragma unroll
-    for (int q = 0; q < 16; q++) Pr[q] = acc[q];
+  for (int r = 0; r < 6; r++)
+#pragma unroll
+    for (int cc = 0; cc < 6; cc++) PT(r, cc) = fma(a[r], b[cc], PT(r, cc));
+}
+template <int K>
+__device__ __forceinline__ void outer_k(double (&Pt)[36], const double* a, int ars, int aks, const double* b, int brs, int bks) {
+  double a0[6], b0[6], a1[6], b1[6];
+  ld6(a0, a, ars);
+  ld6(b0, b, brs);
+#pragma unroll 1
+  for (int k = 0; k + 2 <= K; k += 2) {
+    ld6(a1, a + (k + 1) * aks, ars);
+    ld6(b1, b + (k + 1) * bks, brs);
+    fma66(Pt, a0, b0);
+    if (k + 2 < K) {
+      ld6(a0, a + (k + 2) * aks, ars);
+      ld6(b0, b + (k + 2) * bks, brs);
+    }
+    fma66(Pt, a1, b1);
+  }
+  if (K & 1) fma66(Pt, a0, b0);
+}
+// Pt(r, cc) += sum_q (gr[r * 6 + q] * Qu[q]) * gc[cc * 6 + q], q < 6   (G_d,i Qu G_d,j^T)
+__device__ __forceinline__ void outer_gq(double (&Pt)[36], const double* gr, const double* gc, const double* Qu) {
+  double a0[6], b0[6], a1[6], b1[6];
+  ld6(a0, gr, 6);
+  ld6(b0, gc, 6);
+#pragma unroll 1
+  for (int q = 0; q < 6; q += 2) {
+    ld6(a1, gr + q + 1, 6);
+    ld6(b1, gc + q + 1, 6);
+    {
+      const double qu = Qu[q];
+#pragma unroll
+      for (int r = 0; r < 6; r++) a0[r] *= qu;
+    }
+    fma66(Pt, a0, b0);
+    if (q + 2 < 6) {
+      ld6(a0, gr + q + 2, 6);
+      ld6(b0, gc + q + 2, 6);
+    }
+    {
+      const double qu = Qu[q + 1];
+#pragma unroll
+      for (int r = 0; r < 6; r++) a1[r] *= qu;
+    }
+    fma66(Pt, a1, b1);
   }
 }
 
 // ------------------------------------------------------------------------------------------------------------------
 // PROP: propagate_state (vi_ekf.cpp:262-318) with the structured covariance product
+//   model (x warp, one event ahead): guards, body-frame input, continuous dynamics (phase A)
+//   B   P warps: discretised rows [A_d | G_d], one row per thread                    || x warp: noise values four events ahead
+//   C+D1  P warps: own row of T = A_bb P_bb / Y = A_fb P_bb + A_ff P_fb (old P), then the tile Z = A_ff,i P_ij + A_fb,i P_bf,j
+//                                                                                      || x warp: state boxplus, fix_depth, time
+//   D2  P warps: P'_bb, own row of P'_fb = Y A_bb^T + G_d Qu G_d^T (in place), tile P'_ij = Z A_ff,j^T + Y_i A_fb,j^T + G_d,i Qu G_d,j^T
+//                                                                                      || x warp: the next event's model
 // ------------------------------------------------------------------------------------------------------------------
 template <int TW>
-__device__ __forceinline__ void tile_propagate(TCtx<TW>& c, const KParams& p, const viekf_event& E, double (&Pt)[36]) {
-  constexpr int G = 32 * (TW + 1);
-  double dt;
-  int len;
-  if (!prop_discretise(c, p, E, dt, len, 1)) return;
-  PH(c, 1)
+__device__ __forceinline__ void p_propagate(TCtx<TW>& c, const KParams& p, const double* M, double (&Pt)[36]) {
+  constexpr int PTH = 32 * TW;
+  const int* Mi = (const int*)(M + MD_INT);
+  if (Mi[MI_KIND] != MK_PROP_RUN) return;  // the call does not advance the filter (vi_ekf.cpp:274-290)
+  const double dt = M[MD_DT];
+  const int len = Mi[MI_LEN];
+  const int n = 16 + 3 * len;
   const int lenp = (len + 1) & ~1;
   const int nfr = 3 * lenp;
-  // ---- phase C: one row of Y = A_fb P_bb + A_ff P_fb (3 lenp x 16) or of T = A_bb P_bb per thread ----
-  // (Y rows on the tile warps, T rows on the base warp: no divergent warp)
-  if (!c.basew) {
-    for (int fr = c.tid; fr < nfr; fr += 32 * TW) {
-      const int i = fr / 3;
+  const int npad = 16 + nfr;
+  if (!Mi[MI_PREP]) c.sync();  // phase A could not run ahead (the previous event was a propagate that still read the Y buffer)
+  PH(c, 1)
+  // ---- phase B ----
+  discretise_rows(c, dt, n, npad, c.tid, PTH);
+  PHS(c, 2)
+  // ---- phase C: own rows of T and Y (two column halves: 8 accumulators + two operand rows in flight next to the 72 tile
+  //      registers), and GqT[q][cc] = Qu[q] G_d(cc, q) ----
+  for (int e = c.tid; e < 96; e += PTH) {
+    const int q = e >> 4, cc = e & 15;
+    c.GqT[e] = c.Gd[cc * 6 + q] * p.Qu[q];
+  }
+  for (int r = c.tid; r < npad; r += PTH) {
+    if (r < 16) {
+#pragma unroll 1
+      for (int h = 0; h < 16; h += 8) {
+        double acc[8];
+#pragma unroll
+        for (int q = 0; q < 8; q++) acc[q] = 0.0;
+        rows<8, 16, 1, PBS, true>(acc, c.Abd + r * 16, c.Pbb + h);
+#pragma unroll
+        for (int q = 0; q < 8; q++) c.T[r * 17 + h + q] = acc[q];
+      }
+    } else {
+      const int fr = r - 16, i = fr / 3;
       const double* Ad = c.Afd + fr * 19;
       double* Yr = c.Y + fr * 17;
 #pragma unroll 1
-      for (int h = 0; h < 16; h += 8) {  // two column halves: 8 accumulators + two operand rows in flight next to the 72 tile registers
+      for (int h = 0; h < 16; h += 8) {
         double acc[8];
 #pragma unroll
         for (int q = 0; q < 8; q++) acc[q] = 0.0;
@@ -342,24 +564,10 @@ __device__ __forceinline__ void tile_propagate(TCtx<TW>& c, const KParams& p, co
         for (int q = 0; q < 8; q++) Yr[h + q] = acc[q];
       }
     }
-  } else if (c.lane < 16) {
-    const int r = c.lane;
-    double acc[16];
-#pragma unroll
-    for (int q = 0; q < 16; q++) acc[q] = 0.0;
-    rows<16, 16, 1, PBS, true>(acc, c.Abd + r * 16, c.Pbb);
-#pragma unroll
-    for (int q = 0; q < 16; q++) c.T[r * 17 + q] = acc[q];
-    tile_dead(Pt);
   }
-  PHS(c, 2)
-  // ---- phase D1: tiles: Z = A_ff,i P_ij + A_fb,i P_bf,j (last readers of the old P_fb); base warp: P'_bb in place (T holds
-  //      A_bb P_bb) and the state boxplus ----
+  // ---- phase D1: Z = A_ff,i P_ij + A_fb,i P_bf,j (last readers of the old P_fb) ----
   const bool live_tile = c.tile && 2 * c.ti < len;
   const int R = 6 * c.ti, C = 6 * c.tj;
-  if (c.tid == G - 1 || c.tid < len) boxplus_inplace(c, c.dx, dt, len);  // only the warps with a share make the out-of-line call
-  if (c.tid < len) tile_fix_x(c, p, c.tid);  // phase F of the other executor, by the thread that owns the feature's state
-  if (c.tid == 0) *c.tcur = E.t;
   if (live_tile) {
     // Z = A_ff,i P_ij  (block rows), in place
 #pragma unroll
@@ -376,40 +584,43 @@ __device__ __forceinline__ void tile_propagate(TCtx<TW>& c, const KParams& p, co
         for (int a = 0; a < 3; a++) PT(3 * bi + a, cc) = fma(Af[a * 3 + 2], t2, fma(Af[a * 3 + 1], t1, Af[a * 3] * t0));
       }
     }
-    // Z += A_fb,i P_bf,j   (base columns VEL..MU: 3..15)
-#pragma unroll 1
-    for (int k = 3; k < 16; k++) {
-      double ar[6], bc[6];
-#pragma unroll
-      for (int r = 0; r < 6; r++) ar[r] = c.Afd[(R + r) * 19 + k];
-#pragma unroll
-      for (int cc = 0; cc < 6; cc++) bc[cc] = c.Pfb[(C + cc) * 17 + k];
-#pragma unroll
-      for (int r = 0; r < 6; r++)
-#pragma unroll
-        for (int cc = 0; cc < 6; cc++) PT(r, cc) = fma(ar[r], bc[cc], PT(r, cc));
-    }
-  }
-  if (c.basew) {
-    // P'_bb = T A_bb^T + G_d Qu G_d^T + Qx: lower triangle, mirrored
-    for (int e = c.lane; e < 136; e += 32) {
-      int r = (int)((sqrtf(8.0f * (float)e + 1.0f) - 1.0f) * 0.5f);
-      while (((r + 1) * (r + 2) >> 1) <= e) r++;
-      while (((r * (r + 1)) >> 1) > e) r--;
-      const int cc = e - ((r * (r + 1)) >> 1);
-      double s = 0;
-#pragma unroll
-      for (int k = 0; k < 16; k++) s = fma(c.T[r * 17 + k], c.AbT[k * 16 + cc], s);
-#pragma unroll
-      for (int q = 0; q < 6; q++) s = fma(c.Gd[r * 6 + q] * p.Qu[q], c.Gd[cc * 6 + q], s);
-      if (r == cc) s += p.Qx[r];
-      c.Pbb[r * PBS + cc] = s;
-      c.Pbb[cc * PBS + r] = s;
-    }
-    tile_dead(Pt);
+    // Z += A_fb,i P_bf,j   (base columns VEL..MU: 3..15), operands of column k+1 in flight while the FMAs of column k issue
+    outer_k<13>(Pt, c.Afd + R * 19 + 3, 19, 1, c.Pfb + C * 17 + 3, 17, 1);
   }
   PHS(c, 3)
-  // ---- phase D2: tiles: P'_ij = Z A_ff,j^T + Y_i A_fb,j^T + G_d,i Qu G_d,j^T; base warp: P'_fb = Y A_bb^T + ... in place ----
+  // ---- phase D2 ----
+  // P'_bb = T A_bb^T + G_d Qu G_d^T + Qx: lower triangle, mirrored
+  for (int e = c.tid; e < 136; e += PTH) {
+    int r = (int)((sqrtf(8.0f * (float)e + 1.0f) - 1.0f) * 0.5f);
+    while (((r + 1) * (r + 2) >> 1) <= e) r++;
+    while (((r * (r + 1)) >> 1) > e) r--;
+    const int cc = e - ((r * (r + 1)) >> 1);
+    double s = 0;
+#pragma unroll
+    for (int k = 0; k < 16; k++) s = fma(c.T[r * 17 + k], c.AbT[k * 16 + cc], s);
+#pragma unroll
+    for (int q = 0; q < 6; q++) s = fma(c.Gd[r * 6 + q] * p.Qu[q], c.Gd[cc * 6 + q], s);
+    if (r == cc) s += p.Qx[r];
+    c.Pbb[r * PBS + cc] = s;
+    c.Pbb[cc * PBS + r] = s;
+  }
+  // own row of P'_fb = Y A_bb^T + G_d,f Qu G_d,b^T, in place (D1 was the last reader of the old P_fb)
+  for (int r = 16 + c.tid; r < npad; r += PTH) {
+    const int fr = r - 16;
+    const double* Yr = c.Y + fr * 17;
+    const double* Gr = c.Gd + r * 6;
+    double* Pr = c.Pfb + fr * 17;
+#pragma unroll 1
+    for (int h = 0; h < 16; h += 8) {
+      double acc[8];
+#pragma unroll
+      for (int q = 0; q < 8; q++) acc[q] = 0.0;
+      rows<8, 16, 1, 16, true>(acc, Yr, c.AbT + h);
+      rows<8, 6, 1, 16, true>(acc, Gr, c.GqT + h);
+#pragma unroll
+      for (int q = 0; q < 8; q++) Pr[h + q] = acc[q];
+    }
+  }
   if (live_tile) {
     // O = Z A_ff,j^T  (block columns), in place
 #pragma unroll
@@ -427,32 +638,9 @@ __device__ __forceinline__ void tile_propagate(TCtx<TW>& c, const KParams& p, co
       }
     }
     // O += Y_i A_fb,j^T
-#pragma unroll 1
-    for (int k = 3; k < 16; k++) {
-      double yr[6], ac[6];
-#pragma unroll
-      for (int r = 0; r < 6; r++) yr[r] = c.Y[(R + r) * 17 + k];
-#pragma unroll
-      for (int cc = 0; cc < 6; cc++) ac[cc] = c.Afd[(C + cc) * 19 + k];
-#pragma unroll
-      for (int r = 0; r < 6; r++)
-#pragma unroll
-        for (int cc = 0; cc < 6; cc++) PT(r, cc) = fma(yr[r], ac[cc], PT(r, cc));
-    }
-    // O += G_d,i Qu G_d,j^T
-#pragma unroll 1
-    for (int q = 0; q < 6; q++) {
-      double gr[6], gc[6];
-      const double qu = p.Qu[q];
-#pragma unroll
-      for (int r = 0; r < 6; r++) gr[r] = c.Gd[(16 + R + r) * 6 + q] * qu;
-#pragma unroll
-      for (int cc = 0; cc < 6; cc++) gc[cc] = c.Gd[(16 + C + cc) * 6 + q];
-#pragma unroll
-      for (int r = 0; r < 6; r++)
-#pragma unroll
-        for (int cc = 0; cc < 6; cc++) PT(r, cc) = fma(gr[r], gc[cc], PT(r, cc));
-    }
+    outer_k<13>(Pt, c.Y + R * 17 + 3, 17, 1, c.Afd + C * 19 + 3, 19, 1);
+    // O += (G_d,i Qu) G_d,j^T: the row factor scaled by Qu[q] first, as G_d Qu G_d^T is evaluated everywhere
+    outer_gq(Pt, c.Gd + (16 + R) * 6, c.Gd + (16 + C) * 6, p.Qu);
     if (c.ti == c.tj) {
 #pragma unroll
       for (int bi = 0; bi < 2; bi++)
@@ -463,15 +651,42 @@ __device__ __forceinline__ void tile_propagate(TCtx<TW>& c, const KParams& p, co
     }
     tile_mirror(c, Pt);
   }
-  if (c.basew) {
-    base_pfb(c.Y, c.AbT, c.Gd, c.T, c.Pfb, p.Qu, nfr, c.lane);
-    resolve_next(c, p, 32 * TW);
-    tile_dead(Pt);
-  } else {
-    c.resolved = true;
-  }
   PH(c, 4)
-  // no barrier here: the one that ends the event publishes P'_fb, the resolved values and the pending depth corrections
+  // no barrier here: the one that ends the event publishes P'_bb, P'_fb and the pending depth corrections
+}
+
+// the x warp's part of a propagate
+template <int TW>
+__device__ __forceinline__ void x_propagate(TCtx<TW>& c, const KParams& p, const viekf_event& E, const double* M, int64_t rel, bool& resolved) {
+  const int* Mi = (const int*)(M + MD_INT);
+  const int mk = Mi[MI_KIND];
+  if (mk != MK_PROP_RUN) {  // the call does not advance the filter (vi_ekf.cpp:274-290)
+    if (c.lane == 0) {
+      if (mk == MK_PROP_LATCH) {
+        c.sc[SC_STARTED] = 1;
+        *c.tcur = E.t;
+      } else if (mk == MK_PROP_BACK) {
+        c.sc[SC_FLAGS] |= VIEKF_FLAG_BACKWARD_DT;
+      }
+    }
+    __syncwarp();
+    return;
+  }
+  const double dt = M[MD_DT];
+  const int len = Mi[MI_LEN];
+  if (!Mi[MI_PREP]) {
+    xw_phase_a(c, p, c.sm + SM_UB, len);
+    c.sync();
+  }
+  PH(c, 1)
+  if ((rel & 3) == 0) xw_resolve(c, p, rel + 4);  // idle while the P warps discretise
+  resolved = true;
+  PHS(c, 2)
+  // the state: x <- x [+] xdot dt, fix_depth, time (phases E / F of the other executor)
+  xw_boxplus(c.x, c.dx, dt, len, c.lane);
+  for (int i = c.lane; i < len; i += 32) tile_fix_x(c, p, i);
+  if (c.lane == 0) *c.tcur = E.t;
+  PHS(c, 3)
 }
 
 // ------------------------------------------------------------------------------------------------------------------
@@ -479,6 +694,12 @@ __device__ __forceinline__ void tile_propagate(TCtx<TW>& c, const KParams& p, co
 //   P_ij += (1 - a_i a_j) ( W_i.K_j - K_i.H_j ),   H = P H^T,  K = H S^-1,  W = K S - H,  a = 1 - lambda (partial update) or 0
 // which is the Joseph form (I-KH) P (I-KH)^T + K R K^T - P = K S K^T - K (HP) - (HP)^T K^T with the two terms that share
 // K_j merged.  Vectors live in the update workspace (padding rows are exact zeros).
+//   model (x warp, one event ahead): bookkeeping, h, H, residual
+//   P1  tile + base warps: P H^T rows                      ||  x warp: value resolution
+//   P2  x warp: S = H P H^T + R, S^-1, Mahalanobis gate
+//   P3  tile + base warps: K, W rows, lambda o (K r)
+//   P4  tile warps: rank update of the tiles  ||  base warp: rank update of [P_bb; P_fb]  ||  x warp: state boxplus, fix_depth,
+//       then (in the event loop) the next event's model
 // ------------------------------------------------------------------------------------------------------------------
 struct TUpdVec {
   double2 *Kv, *Hv, *Wv;
@@ -509,225 +730,183 @@ __device__ __forceinline__ double rank_delta(double2 wr, double2 kr, double w2r,
   return d;
 }
 
-// rows of [P_bb; P_fb]: one row per lane, three rows per pass; column vectors are warp broadcasts (out of line: see base_pfb)
+// own row r of [P_bb; P_fb] (16 columns): the row goes to registers, the column vectors are warp broadcasts
 template <int RD>
-static __device__ __noinline__ void base_rank(TUpdVec v, double* Pbb, double* Pfb, int npad, int lane) {
-  constexpr int NR = 3;
-  // every pointer is into shared memory: lets the compiler emit LDS / STS instead of generic loads and stores
-  __builtin_assume(__isShared(Pbb));
-  __builtin_assume(__isShared(Pfb));
-  __builtin_assume(__isShared(v.Kv));
-  __builtin_assume(__isShared(v.Hv));
-  __builtin_assume(__isShared(v.Wv));
-  __builtin_assume(__isShared(v.K2));
-  __builtin_assume(__isShared(v.H2));
-  __builtin_assume(__isShared(v.W2));
-  __builtin_assume(__isShared(v.av));
-  for (int ib = lane; ib < npad; ib += 32 * NR) {
-    double2 wr[NR], kr[NR];
-    double ar[NR], w2r[NR], k2r[NR];
-    double* prow[NR];
-    int jmax[NR], ii[NR];
+__device__ __forceinline__ void p_row_rank(const TUpdVec& v, double* Pbb, double* Pfb, int r) {
+  const double2 wr = v.Wv[r], kr = v.Kv[r];
+  const double ar = v.av[r];
+  const double w2r = (RD == 3) ? v.W2[r] : 0.0, k2r = (RD == 3) ? v.K2[r] : 0.0;
+  double* prow = (r < 16) ? Pbb + r * PBS : Pfb + (r - 16) * 17;
+  const int jmax = (r < 16) ? r : 15;
+  double pr[16];
 #pragma unroll
-    for (int m = 0; m < NR; m++) {
-      const int i = ib + 32 * m;
-      const bool valid = i < npad;
-      ii[m] = valid ? i : 0;
-      wr[m] = v.Wv[ii[m]];
-      kr[m] = v.Kv[ii[m]];
-      ar[m] = v.av[ii[m]];
-      w2r[m] = (RD == 3) ? v.W2[ii[m]] : 0.0;
-      k2r[m] = (RD == 3) ? v.K2[ii[m]] : 0.0;
-      prow[m] = (ii[m] < 16) ? Pbb + ii[m] * PBS : Pfb + (ii[m] - 16) * 17;
-      jmax[m] = valid ? (ii[m] < 16 ? ii[m] : 15) : -1;
-    }
-    // the three rows go to registers first (immediate-offset loads, no per-column address arithmetic), then 16 fully
-    // unrolled columns: column vectors are warp broadcasts, the three rows give independent FMA chains
-    double pr[NR][16];
+  for (int j = 0; j < 16; j++) pr[j] = prow[j];
 #pragma unroll
-    for (int m = 0; m < NR; m++)
+  for (int j = 0; j < 16; j++) {
+    const double2 kj = v.Kv[j], hj = v.Hv[j];
+    const double aj = v.av[j];
+    const double k2j = (RD == 3) ? v.K2[j] : 0.0, h2j = (RD == 3) ? v.H2[j] : 0.0;
+    const double d = rank_delta<RD>(wr, kr, w2r, k2r, kj, hj, k2j, h2j);
+    const double u = fma(-ar, aj, 1.0);
+    pr[j] = fma(d, u, pr[j]);
+  }
+  // P_bb keeps both halves: the owner of row r writes (r, j) and its mirror (j, r) for j <= r; what it read above the
+  // diagonal is recomputed but never stored
 #pragma unroll
-      for (int j = 0; j < 16; j++) pr[m][j] = prow[m][j];
-#pragma unroll
-    for (int j = 0; j < 16; j++) {
-      const double2 kj = v.Kv[j], hj = v.Hv[j];
-      const double aj = v.av[j];
-      const double k2j = (RD == 3) ? v.K2[j] : 0.0, h2j = (RD == 3) ? v.H2[j] : 0.0;
-#pragma unroll
-      for (int m = 0; m < NR; m++) {
-        const double d = rank_delta<RD>(wr[m], kr[m], w2r[m], k2r[m], kj, hj, k2j, h2j);
-        const double u = fma(-ar[m], aj, 1.0);
-        pr[m][j] = fma(d, u, pr[m][j]);
-      }
-    }
-#pragma unroll
-    for (int m = 0; m < NR; m++)
-#pragma unroll
-      for (int j = 0; j < 16; j++) {
-        const bool ok = j <= jmax[m];
-        if (ok) prow[m][j] = pr[m][j];
-        if (ok && ii[m] < 16) Pbb[j * PBS + ii[m]] = pr[m][j];
-      }
+  for (int j = 0; j < 16; j++) {
+    const bool ok = j <= jmax;
+    if (ok) prow[j] = pr[j];
+    if (ok && r < 16) Pbb[j * PBS + r] = pr[j];
   }
 }
 
 template <int TW, int RD>
-__device__ __forceinline__ int tile_update_core(TCtx<TW>& c, const KParams& p, const viekf_event& E, int n, int len, const HReg& H,
-                                                double (&Pt)[36]) {
-  constexpr int G = 32 * (TW + 1);
+__device__ __forceinline__ int p_update(TCtx<TW>& c, const KParams& p, const double* M, double (&Pt)[36]) {
+  constexpr int PTH = 32 * TW;  // threads that own covariance rows
   constexpr int MC = 6;
-  int* cols = c.sc + SC_COUNT;
+  const int* Mi = (const int*)(M + MD_INT);
+  int* Gi = (int*)(c.gate + GD_INT);
+  const int len = Mi[MI_LEN];
   const int lenp = (len + 1) & ~1;
   const int npad = 16 + 3 * lenp;
-  TUpdVec v(c.upd, 16 + 3 * ((p.N + 1) & ~1));
+  const int m = Mi[MI_M];
+  TUpdVec v(c.upd, 16 + 6 * ((tile_cap<TW>() + 1) / 2));
   PH(c, 8)
-  const bool featcols = (H.m > 0) && (H.col[0] >= 16);  // every H touches either base columns or the columns of one feature
-  // ---- P H^T ----
-  if (!featcols) {
-    for (int i = c.tid; i < npad; i += G) {
-      double s[3] = {0, 0, 0};
+  // ---- P1: P H^T ----
+  {
+    double h[RD][MC];
+    int col[MC];
 #pragma unroll
-      for (int k = 0; k < MC; k++)
-        if (k < H.m) {
-          const double pv = (i < 16) ? c.Pbb[i * PBS + H.col[k]] : c.Pfb[(i - 16) * 17 + H.col[k]];
+    for (int k = 0; k < MC; k++) {
+      col[k] = Mi[MI_COL + k];
 #pragma unroll
-          for (int a = 0; a < RD; a++) s[a] = fma(pv, H.h[a * MC + k], s[a]);
-        }
-      v.Hv[i] = make_double2(s[0], s[1]);
-      if (RD == 3) v.H2[i] = s[2];
+      for (int a = 0; a < RD; a++) h[a][k] = M[MD_H + a * MC + k];
     }
-  } else {
-    const int fi = (H.col[0] - 16) / 3, tb = fi >> 1, sb = fi & 1;
-    // effective 3-column Jacobian of the feature block: he[a][kk] = sum over the k with local column kk
-    double he[RD][3];
+    const bool featcols = (m > 0) && (col[0] >= 16);  // every H touches either base columns or the columns of one feature
+    if (!featcols) {
+      for (int i = c.tid; i < npad; i += PTH) {
+        double s[3] = {0, 0, 0};
 #pragma unroll
-    for (int a = 0; a < RD; a++)
+        for (int k = 0; k < MC; k++)
+          if (k < m) {
+            const double pv = (i < 16) ? c.Pbb[i * PBS + col[k]] : c.Pfb[(i - 16) * 17 + col[k]];
 #pragma unroll
-      for (int kk = 0; kk < 3; kk++) he[a][kk] = 0.0;
-#pragma unroll
-    for (int k = 0; k < 2; k++)  // feature-column models have at most two live columns (FEAT, QZETA: 2; DEPTH, INV_DEPTH: 1)
-      if (k < H.m) {
-        const int lk = H.col[k] - 16 - 3 * fi;
-#pragma unroll
-        for (int a = 0; a < RD; a++)
-#pragma unroll
-          for (int kk = 0; kk < 3; kk++)
-            if (lk == kk) he[a][kk] += H.h[a * MC + k];
-      }
-    if (c.basew && c.lane < 16) {
-      const int i = c.lane;
-      double s[3] = {0, 0, 0};
-#pragma unroll
-      for (int kk = 0; kk < 3; kk++) {
-        const double pv = c.Pfb[(3 * fi + kk) * 17 + i];
-#pragma unroll
-        for (int a = 0; a < RD; a++) s[a] = fma(pv, he[a][kk], s[a]);
-      }
-      v.Hv[i] = make_double2(s[0], s[1]);
-      if (RD == 3) v.H2[i] = s[2];
-    }
-    if (c.tile && 2 * c.ti < len) {
-      if (c.tj == tb) {  // rows of this tile against the columns of feature fi
-#pragma unroll
-        for (int r = 0; r < 6; r++) {
-          double s[3] = {0, 0, 0};
-#pragma unroll
-          for (int kk = 0; kk < 3; kk++) {
-            const double pv = sb ? PT(r, 3 + kk) : PT(r, kk);
-#pragma unroll
-            for (int a = 0; a < RD; a++) s[a] = fma(pv, he[a][kk], s[a]);
+            for (int a = 0; a < RD; a++) s[a] = fma(pv, h[a][k], s[a]);
           }
-          v.Hv[16 + 6 * c.ti + r] = make_double2(s[0], s[1]);
-          if (RD == 3) v.H2[16 + 6 * c.ti + r] = s[2];
+        v.Hv[i] = make_double2(s[0], s[1]);
+        if (RD == 3) v.H2[i] = s[2];
+      }
+    } else {
+      const int fi = (col[0] - 16) / 3, tb = fi >> 1, sb = fi & 1;
+      // effective 3-column Jacobian of the feature block: he[a][kk] = sum over the k with local column kk
+      double he[RD][3];
+#pragma unroll
+      for (int a = 0; a < RD; a++)
+#pragma unroll
+        for (int kk = 0; kk < 3; kk++) he[a][kk] = 0.0;
+#pragma unroll
+      for (int k = 0; k < 2; k++)  // feature-column models have at most two live columns (FEAT, QZETA: 2; DEPTH, INV_DEPTH: 1)
+        if (k < m) {
+          const int lk = col[k] - 16 - 3 * fi;
+#pragma unroll
+          for (int a = 0; a < RD; a++)
+#pragma unroll
+            for (int kk = 0; kk < 3; kk++)
+              if (lk == kk) he[a][kk] += h[a][k];
         }
-      } else if (c.ti == tb) {  // columns of this tile against the rows of feature fi (symmetry)
+      if (c.tid < 16) {
+        const int i = c.tid;
+        double s[3] = {0, 0, 0};
 #pragma unroll
-        for (int cc = 0; cc < 6; cc++) {
-          double s[3] = {0, 0, 0};
+        for (int kk = 0; kk < 3; kk++) {
+          const double pv = c.Pfb[(3 * fi + kk) * 17 + i];
 #pragma unroll
-          for (int kk = 0; kk < 3; kk++) {
-            const double pv = sb ? PT(3 + kk, cc) : PT(kk, cc);
+          for (int a = 0; a < RD; a++) s[a] = fma(pv, he[a][kk], s[a]);
+        }
+        v.Hv[i] = make_double2(s[0], s[1]);
+        if (RD == 3) v.H2[i] = s[2];
+      }
+      if (c.tile && 2 * c.ti < len) {
+        if (c.tj == tb) {  // rows of this tile against the columns of feature fi
 #pragma unroll
-            for (int a = 0; a < RD; a++) s[a] = fma(pv, he[a][kk], s[a]);
+          for (int r = 0; r < 6; r++) {
+            double s[3] = {0, 0, 0};
+#pragma unroll
+            for (int kk = 0; kk < 3; kk++) {
+              const double pv = sb ? PT(r, 3 + kk) : PT(r, kk);
+#pragma unroll
+              for (int a = 0; a < RD; a++) s[a] = fma(pv, he[a][kk], s[a]);
+            }
+            v.Hv[16 + 6 * c.ti + r] = make_double2(s[0], s[1]);
+            if (RD == 3) v.H2[16 + 6 * c.ti + r] = s[2];
           }
-          v.Hv[16 + 6 * c.tj + cc] = make_double2(s[0], s[1]);
-          if (RD == 3) v.H2[16 + 6 * c.tj + cc] = s[2];
+        } else if (c.ti == tb) {  // columns of this tile against the rows of feature fi (symmetry)
+#pragma unroll
+          for (int cc = 0; cc < 6; cc++) {
+            double s[3] = {0, 0, 0};
+#pragma unroll
+            for (int kk = 0; kk < 3; kk++) {
+              const double pv = sb ? PT(3 + kk, cc) : PT(kk, cc);
+#pragma unroll
+              for (int a = 0; a < RD; a++) s[a] = fma(pv, he[a][kk], s[a]);
+            }
+            v.Hv[16 + 6 * c.tj + cc] = make_double2(s[0], s[1]);
+            if (RD == 3) v.H2[16 + 6 * c.tj + cc] = s[2];
+          }
         }
       }
     }
   }
-  if (c.tid == 0) cols[8] = H.hnan ? 1 : 0;
   PHS(c, 9)
-  // ---- S = H P H^T + R, S^-1, Mahalanobis gate: every thread evaluates the same registers ----
-  double S[3][3], Si[3][3];
+  PHS(c, 10)  // the x warp evaluates S^-1 and the gate between these two barriers
+  if (Gi[GI_GATED]) return VIEKF_MEAS_GATED;  // early return: no fix_depth (vi_ekf_meas.cpp:238)
+  // ---- P3: K = P H^T S^-1, W = K S - P H^T, state correction lambda o (K r) ----
   {
-    double ph[MC][3];
+    double S[3][3], Si[3][3];
 #pragma unroll
-    for (int k = 0; k < MC; k++) {
-      const int ck = (k < H.m) ? H.col[k] : 0;
-      const double2 t = v.Hv[ck];
-      ph[k][0] = t.x;
-      ph[k][1] = t.y;
-      ph[k][2] = (RD == 3) ? v.H2[ck] : 0.0;
+    for (int a = 0; a < RD; a++) {
+#pragma unroll
+      for (int b = 0; b < RD; b++) {
+        Si[a][b] = c.gate[GD_SI + a * 3 + b];
+        S[a][b] = c.gate[GD_S + a * 3 + b];
+      }
     }
-#pragma unroll
-    for (int a = 0; a < RD; a++)
+    bool bad = false;
+    for (int i = c.tid; i < npad; i += PTH) {
+      const double2 h01 = v.Hv[i];
+      double ph[3] = {h01.x, h01.y, 0.0};
+      if (RD == 3) ph[2] = v.H2[i];
+      double k3[3] = {0, 0, 0}, w3[3] = {0, 0, 0};
 #pragma unroll
       for (int b = 0; b < RD; b++) {
         double s = 0;
 #pragma unroll
-        for (int k = 0; k < MC; k++)
-          if (k < H.m) s += H.h[a * MC + k] * ph[k][b];
-        S[a][b] = s + E.R[a + b * RD];
+        for (int a = 0; a < RD; a++) s += ph[a] * Si[a][b];
+        k3[b] = s;
+        bad |= (s != s);
       }
-  }
-  const double mahal = inverse_and_mahal<RD>(S, Si, H.res);
-  if (mahal > 9.0) {
-    if (c.tid == 0) c.sc[SC_NGATED] += 1;
-    return VIEKF_MEAS_GATED;  // early return: no fix_depth (vi_ekf_meas.cpp:238)
-  }
-  // ---- K = P H^T S^-1, W = K S - P H^T, state correction lambda o (K r) ----
-  bool bad = false;
-  for (int i = c.tid; i < npad; i += G) {
-    const double2 h01 = v.Hv[i];
-    double ph[3] = {h01.x, h01.y, 0.0};
-    if (RD == 3) ph[2] = v.H2[i];
-    double k3[3] = {0, 0, 0}, w3[3] = {0, 0, 0};
 #pragma unroll
-    for (int b = 0; b < RD; b++) {
-      double s = 0;
+      for (int a = 0; a < RD; a++) {
+        double s = 0;
 #pragma unroll
-      for (int a = 0; a < RD; a++) s += ph[a] * Si[a][b];
-      k3[b] = s;
-      bad |= (s != s);
+        for (int b = 0; b < RD; b++) s += k3[b] * S[b][a];
+        w3[a] = s - ph[a];
+      }
+      v.Kv[i] = make_double2(k3[0], k3[1]);
+      v.Wv[i] = make_double2(w3[0], w3[1]);
+      if (RD == 3) {
+        v.K2[i] = k3[2];
+        v.W2[i] = w3[2];
+      }
+      v.av[i] = p.use_partial ? 1.0 - c.lam[i] : 0.0;
     }
-    double d = 0;
-#pragma unroll
-    for (int a = 0; a < RD; a++) d += k3[a] * H.res[a];
-#pragma unroll
-    for (int a = 0; a < RD; a++) {
-      double s = 0;
-#pragma unroll
-      for (int b = 0; b < RD; b++) s += k3[b] * S[b][a];
-      w3[a] = s - ph[a];
-    }
-    v.Kv[i] = make_double2(k3[0], k3[1]);
-    v.Wv[i] = make_double2(w3[0], w3[1]);
-    if (RD == 3) {
-      v.K2[i] = k3[2];
-      v.W2[i] = w3[2];
-    }
-    const double li = c.lam[i];
-    v.av[i] = p.use_partial ? 1.0 - li : 0.0;
-    c.dx[i] = p.use_partial ? li * d : d;
+    if (bad) atomicOr((unsigned*)&Gi[GI_NAN], 1u);
   }
-  if (bad) atomicOr((unsigned*)&cols[8], 1u);
-  PHS(c, 10)
-  if (!cols[8]) {
-    // base part on the spare lane of the last tile warp (the base warp has the longer rank update); warps without a share of the
-    // boxplus skip the out-of-line call altogether
-    if (c.tid == 32 * TW - 1 || c.tid < len) boxplus_inplace(c, c.dx, 1.0, len, 32 * TW - 1);
-    PH(c, 12)
+  PH(c, 11)
+  c.psync();  // the x warp forms the state correction lambda o (K r) itself and is already applying it
+  PH(c, 11 + 32)
+  // ---- P4: rank update of the own tile and the own row(s) of [P_bb; P_fb] ----
+  if (!Gi[GI_NAN]) {
     if (c.tile && 2 * c.ti < len) {
       const int R = 16 + 6 * c.ti, C = 16 + 6 * c.tj;
       // three columns at a time: 72 tile registers + 3 column vectors + 1 row vector stay inside the register budget
@@ -759,18 +938,105 @@ __device__ __forceinline__ int tile_update_core(TCtx<TW>& c, const KParams& p, c
       tile_mirror(c, Pt);
     }
     PH(c, 13)
-    resolve_next(c, p, 32);
-    if (c.basew) {
-      base_rank<RD>(v, c.Pbb, c.Pfb, npad, c.lane);
-      PH(c, 14)
-      tile_dead(Pt);
+    for (int r = c.tid; r < npad; r += PTH) p_row_rank<RD>(v, c.Pbb, c.Pfb, r);
+    PH(c, 14)
+  }
+  return VIEKF_MEAS_SUCCESS;
+}
+
+// the x warp's part of an update: S^-1 and the gate between the gain barriers, then the state correction
+template <int TW, int RD>
+__device__ __forceinline__ int x_update(TCtx<TW>& c, const KParams& p, const viekf_event& E, const double* M, int64_t rel, bool& resolved) {
+  constexpr int MC = 6;
+  const int* Mi = (const int*)(M + MD_INT);
+  int* Gi = (int*)(c.gate + GD_INT);
+  const int len = Mi[MI_LEN];
+  const int m = Mi[MI_M];
+  TUpdVec v(c.upd, 16 + 6 * ((tile_cap<TW>() + 1) / 2));
+  PH(c, 8)
+  if ((rel & 3) == 0) xw_resolve(c, p, rel + 4);  // idle while the P warps form P H^T
+  resolved = true;
+  PHS(c, 9)
+  // ---- P2: S = H P H^T + R, S^-1 (partial-pivot LU), Mahalanobis gate (vi_ekf_meas.cpp:232-239) ----
+  double S[3][3], Si[3][3], res[3];
+  bool gated;
+  {
+    {
+      double ph[MC][3];
+#pragma unroll
+      for (int k = 0; k < MC; k++) {
+        const int ck = (k < m) ? Mi[MI_COL + k] : 0;
+        const double2 t = v.Hv[ck];
+        ph[k][0] = t.x;
+        ph[k][1] = t.y;
+        ph[k][2] = (RD == 3) ? v.H2[ck] : 0.0;
+      }
+#pragma unroll
+      for (int a = 0; a < RD; a++)
+#pragma unroll
+        for (int b = 0; b < RD; b++) {
+          double s = 0;
+#pragma unroll
+          for (int k = 0; k < MC; k++)
+            if (k < m) s += M[MD_H + a * MC + k] * ph[k][b];
+          S[a][b] = s + E.R[a + b * RD];
+        }
     }
-  } else if (c.tid == 0) {
+#pragma unroll
+    for (int a = 0; a < 3; a++) res[a] = M[MD_RES + a];
+    const double mahal = inverse_and_mahal<RD>(S, Si, res);
+    gated = mahal > 9.0;
+    if (c.lane == 0) {
+#pragma unroll
+      for (int a = 0; a < RD; a++)
+#pragma unroll
+        for (int b = 0; b < RD; b++) {
+          c.gate[GD_SI + a * 3 + b] = Si[a][b];
+          c.gate[GD_S + a * 3 + b] = S[a][b];
+        }
+      Gi[GI_GATED] = gated ? 1 : 0;
+      Gi[GI_NAN] = Mi[MI_HNAN];
+      if (gated) c.sc[SC_NGATED] += 1;
+    }
+  }
+  PHS(c, 10)
+  if (gated) return VIEKF_MEAS_GATED;
+  // ---- the state correction lambda o (K r), K = P H^T S^-1 row by row (the same arithmetic as the P warps' K rows): the x warp
+  //      does not wait for them ----
+  bool bad = Mi[MI_HNAN] != 0;
+  {
+    const int npad = 16 + 3 * ((len + 1) & ~1);
+    for (int i = c.lane; i < npad; i += 32) {
+      const double2 h01 = v.Hv[i];
+      double ph[3] = {h01.x, h01.y, 0.0};
+      if (RD == 3) ph[2] = v.H2[i];
+      double k3[3] = {0, 0, 0};
+#pragma unroll
+      for (int b = 0; b < RD; b++) {
+        double s = 0;
+#pragma unroll
+        for (int a = 0; a < RD; a++) s += ph[a] * Si[a][b];
+        k3[b] = s;
+        bad |= (s != s);
+      }
+      double d = 0;
+#pragma unroll
+      for (int a = 0; a < RD; a++) d += k3[a] * res[a];
+      c.dx[i] = p.use_partial ? c.lam[i] * d : d;
+    }
+  }
+  bad = __any_sync(0xffffffffu, bad);
+  __syncwarp();  // the dx rows of all lanes are visible to the boxplus below
+  PH(c, 11)
+  if (!bad) {
+    xw_boxplus(c.x, c.dx, 1.0, len, c.lane);
+  } else if (c.lane == 0) {  // NO_NANS(K) && NO_NANS(H) failed: the correction is skipped (vi_ekf_meas.cpp:247)
     c.sc[SC_FLAGS] |= VIEKF_FLAG_NAN_GAIN;
     c.sc[SC_NNAN] += 1;
   }
-  if (c.tid < len) tile_fix_x(c, p, c.tid);
-  PH(c, 11)
+  __syncwarp();
+  for (int i = c.lane; i < len; i += 32) tile_fix_x(c, p, i);
+  PH(c, 12)
   return VIEKF_MEAS_SUCCESS;
 }
 
@@ -778,7 +1044,8 @@ __device__ __forceinline__ int tile_update_core(TCtx<TW>& c, const KParams& p, c
 // feature management
 // ------------------------------------------------------------------------------------------------------------------
 // init_feature (vi_ekf_feat.cpp:6-47).  Returns (uniformly) whether a slot was available.
-template <int TW>
+// TILE = false: the x warp's instantiation of a handler (it takes part in the barriers and in the shared-memory work, owns no tile)
+template <int TW, bool TILE>
 __device__ __forceinline__ bool tile_init_feature(TCtx<TW>& c, const KParams& p, double l0, double l1, double depth, double (&Pt)[36]) {
   constexpr int G = 32 * (TW + 1);
   const int len = c.sc[SC_LEN];
@@ -801,7 +1068,7 @@ __device__ __forceinline__ bool tile_init_feature(TCtx<TW>& c, const KParams& p,
   }
   // covariance: rows / columns of the new feature (and of the padding feature that shares its tile row) zero, P0_feat on the diagonal
   const int tb = len >> 1, sb = len & 1;
-  if (c.tile && c.ti == tb) {
+  if (TILE && c.tile && c.ti == tb) {
 #pragma unroll
     for (int r = 0; r < 6; r++)
 #pragma unroll
@@ -827,11 +1094,11 @@ __device__ __forceinline__ bool tile_init_feature(TCtx<TW>& c, const KParams& p,
 
 // Order-preserving removal of features: new feature f <- old feature smap[f], f < newlen (clear_feature, vi_ekf_feat.cpp:50-73,
 // applied once for all removals).  Tiles and P_fb go through the filter's packed P in global memory; x and ids through registers.  Precondition: smap[] published by a barrier.
-template <int TW>
+template <int TW, bool TILE>
 __device__ __forceinline__ void tile_compact(TCtx<TW>& c, const KParams& p, int len, int newlen, double (&Pt)[36]) {
   constexpr int G = 32 * (TW + 1);
   double* gP = p.P + c.b * p.ps;
-  tile_store(c, gP, Pt, len);
+  if (TILE) tile_store(c, gP, Pt, len);
   double xf[5];
   int idv = 0;
   if (c.tid < newlen) {
@@ -855,12 +1122,12 @@ __device__ __forceinline__ void tile_compact(TCtx<TW>& c, const KParams& p, int 
     for (int k = 0; k < 5; k++) c.x[17 + 5 * c.tid + k] = xf[k];
     c.ids[c.tid] = idv;
   }
-  tile_load(c, gP, Pt, newlen, true);
+  if (TILE) tile_load(c, gP, Pt, newlen, true);
   if (c.tid == 0) c.sc[SC_LEN] = newlen;
   c.sync();
 }
 
-template <int TW>
+template <int TW, bool TILE>
 __device__ __forceinline__ void tile_clear_feature(TCtx<TW>& c, const KParams& p, int local, double (&Pt)[36]) {
   constexpr int G = 32 * (TW + 1);
   const int len = c.sc[SC_LEN];
@@ -868,7 +1135,7 @@ __device__ __forceinline__ void tile_clear_feature(TCtx<TW>& c, const KParams& p
   c.sync();
   for (int f = c.tid; f < len - 1; f += G) c.smap[f] = f + (f >= local ? 1 : 0);
   c.sync();
-  tile_compact(c, p, len, len - 1, Pt);
+  tile_compact<TW, TILE>(c, p, len, len - 1, Pt);
 }
 
 // packed lower triangle of P_bb into the T buffer (idle outside propagate): the statistics and the keyframe-reset pose code
@@ -906,7 +1173,7 @@ __device__ __forceinline__ void tile_keyframe_reset(TCtx<TW>& c, const KParams& 
 #pragma unroll
     for (int a = 0; a < 3; a++) row[6 + a] = Nb[a * 3] * v[0] + Nb[a * 3 + 1] * v[1] + Nb[a * 3 + 2] * v[2];
   }
-  if (c.basew) {
+  if ((c.tid >> 5) == 0) {  // warp 0: P_bb, one row / column per lane
     const int l = c.lane;
     if (l < 16) {  // right factor N^T, one row per lane
       double* row = c.Pbb + l * PBS;
@@ -938,7 +1205,7 @@ __device__ __forceinline__ void tile_keyframe_reset(TCtx<TW>& c, const KParams& 
 }
 
 // keep_only_features (vi_ekf_feat.cpp:81-142)
-template <int TW>
+template <int TW, bool TILE>
 __device__ __forceinline__ void tile_keep_only(TCtx<TW>& c, const KParams& p, const int32_t* feats, int nf, double (&Pt)[36]) {
   constexpr int G = 32 * (TW + 1);
   c.sync();
@@ -971,7 +1238,7 @@ __device__ __forceinline__ void tile_keep_only(TCtx<TW>& c, const KParams& p, co
   c.sync();
   const int newlen = c.sc[SC_TMP0];
   const int overlap = c.sc[SC_TMP1];
-  if (newlen < len) tile_compact(c, p, len, newlen, Pt);
+  if (newlen < len) tile_compact<TW, TILE>(c, p, len, newlen, Pt);
   const bool reset = p.use_kfreset && nkf > 0 && ((double)overlap / (double)nkf < p.kf_thresh);
   if (reset) tile_keyframe_reset(c, p);
   c.sync();  // every thread has taken the (uniform) reset decision from the old list size before thread 0 replaces it
@@ -986,7 +1253,7 @@ __device__ __forceinline__ void tile_keep_only(TCtx<TW>& c, const KParams& p, co
 
 // NaNsInTheHouse (vi_ekf_error.cpp:6-19), this thread's share: live x, P_bb, live rows of P_fb, and the owner's tile (entries
 // of a padding feature are exact zeros)
-template <int TW>
+template <int TW, bool TILE>
 __device__ __forceinline__ bool tile_nan_scan(const TCtx<TW>& c, const double (&Pt)[36]) {
   constexpr int G = 32 * (TW + 1);
   const int len = c.sc[SC_LEN];
@@ -1000,27 +1267,126 @@ __device__ __forceinline__ bool tile_nan_scan(const TCtx<TW>& c, const double (&
     const double v = c.Pfb[(e >> 4) * 17 + (e & 15)];
     bad |= (v != v);
   }
-  if (c.tile && 2 * c.ti < len) {
+  if (TILE && c.tile && 2 * c.ti < len) {
 #pragma unroll
     for (int i = 0; i < 36; i++) bad |= (Pt[i] != Pt[i]);
   }
   return bad;
 }
 
-template <int TW>
-struct TileCore {
-  TCtx<TW>& c;
-  const KParams& p;
-  double (&Pt)[36];
-  template <int RD>
-  __device__ __forceinline__ int run(const viekf_event& E, int n, int len, const HReg& H) {
-    return tile_update_core<TW, RD>(c, p, E, n, len, H, Pt);
+// ------------------------------------------------------------------------------------------------------------------
+// The event loop.  One handler per event kind and role; `TILE` selects the P role (owns a tile, Pt) or the x role.  Both roles
+// execute the same sequence of group barriers for every event.
+// ------------------------------------------------------------------------------------------------------------------
+// the handlers that reshuffle the filter (all G threads cooperate; rare next to PROP / UPD)
+template <int TW, bool TILE>
+__device__ __forceinline__ int generic_event(TCtx<TW>& c, const KParams& p, const viekf_event& E, int kind, int64_t ginst, double (&Pt)[36]) {
+  int result = VIEKF_MEAS_NONE;
+  switch (kind) {
+    case VIEKF_EV_INIT:
+      result = tile_init_feature<TW, TILE>(c, p, c.zv[0], c.zv[1], E.z[4], Pt) ? 1 : 0;
+      break;
+    case VIEKF_EV_CLEAR:
+      tile_clear_feature<TW, TILE>(c, p, find_feature(c, E.id), Pt);
+      break;
+    case VIEKF_EV_KEEP:
+      tile_keep_only<TW, TILE>(c, p, p.id_pool + E.ids_off, E.n_ids, Pt);
+      break;
+    case VIEKF_EV_KFRESET:
+      tile_keyframe_reset(c, p);
+      break;
+    case VIEKF_EV_STAT:
+      c.sync();
+      tile_pack_base(c);
+      c.sync();
+      ev_stat(c, p, E, ginst, [&]() { return tile_nan_scan<TW, TILE>(c, Pt); });
+      break;
+    default:
+      break;
   }
-  __device__ __forceinline__ bool init_feature(double l0, double l1, double depth) { return tile_init_feature(c, p, l0, l1, depth, Pt); }
-  __device__ __forceinline__ void fix_depth(int len) {
-    if (c.tid < len) tile_fix_x(c, p, c.tid);
+  return result;
+}
+
+// The x role: the state chain of one filter slot of the CTA, for every filter that slot processes.  Out of line: its registers
+// (no tile) are allocated separately from the kernel body.
+template <int TW, int FPC>
+static __device__ __noinline__ void x_role(const KParams& p, double* base, int gi, int lane) {
+  constexpr int G = 32 * (TW + 1);
+  constexpr int EVW = (int)(sizeof(viekf_event) / sizeof(double));
+  static_assert(sizeof(viekf_event) % sizeof(double) == 0 && EVW <= 32, "viekf_event must fit one warp of doubles");
+  TCtx<TW> c;
+  init_tctx(c, base);
+  c.gi = gi;
+  c.tid = G - 32 + lane;
+  c.lane = lane;
+  c.tile = false;
+  c.xw = true;
+  c.ti = c.tj = 0;
+  double Pz[36];  // never touched: every TILE = false handler skips the tile parts
+  PH_INIT(c)
+  for (int64_t b0 = (int64_t)blockIdx.x * FPC; b0 < p.B; b0 += (int64_t)gridDim.x * FPC) {
+    const bool active = b0 + gi < p.B;
+    const int64_t b = active ? b0 + gi : 0;
+    c.b = b;
+    const int64_t ginst = p.inst_off + b;
+    c.ginst = ginst;
+    c.sync();  // the previous filter of this slot has been stored
+    // while the P warps load the filter: stage the first two event records, resolve the per-instance values of the first four events
+    for (int r = 0; r < 2; r++)
+      if (r < p.ev_count && lane < EVW) c.evb[32 * r + lane] = __ldg((const double*)(p.ev + p.ev_first + r) + lane);
+    xw_resolve(c, p, 0);
+    PHS(c, 0)
+    if (active && p.ev_count > 0) xw_prepare<TW>(p, base, gi, lane, b, 0, -1);
+    c.sync();
+    for (int64_t rel = 0; rel < p.ev_count; rel++) {
+      const int64_t e = p.ev_first + rel;
+      const viekf_event& E = *(const viekf_event*)(c.evb + 32 * (int)(rel & (EVSLOTS - 1)));
+      const double* Mod = c.model + MD_SIZE * (int)(rel & 1);
+      // the record two events ahead is fetched now (one double per lane) and staged before the barrier that ends this event
+      double ev_next = 0.0;
+      const bool stage = (rel + 2 < p.ev_count) && lane < EVW;
+      if (stage) ev_next = __ldg((const double*)(p.ev + e + 2) + lane);
+      const int kind = E.kind;
+      c.zv = c.zvr + 8 * (int)(rel & 7);
+      bool resolved = false;
+      if (active) {
+        if (kind == VIEKF_EV_PROP) {
+          x_propagate(c, p, E, Mod, rel, resolved);
+        } else if (kind == VIEKF_EV_UPD) {
+          const int mk = ((const int*)(Mod + MD_INT))[MI_KIND];
+          if (mk == MK_NEWFEAT) {
+            tile_init_feature<TW, false>(c, p, c.zv[0], c.zv[1], E.z[4], Pz);
+          } else if (mk == MK_INACTIVE) {
+            const int len = c.sc[SC_LEN];
+            for (int i = lane; i < len; i += 32) tile_fix_x(c, p, i);
+          } else if (mk == MK_RUN) {
+            const int rd = E.rdim;  // one call site per residual dimension
+            if (rd == 1) x_update<TW, 1>(c, p, E, Mod, rel, resolved);
+            else if (rd == 2) x_update<TW, 2>(c, p, E, Mod, rel, resolved);
+            else x_update<TW, 3>(c, p, E, Mod, rel, resolved);
+          }
+        } else {
+          generic_event<TW, false>(c, p, E, kind, ginst, Pz);
+        }
+        // noise values four events ahead (if the handler had no idle slot for it), then the next event's model, while the P warps
+        // finish this event.  Every handler that changes x / ids / len on other warps ends with a group barrier.
+        __syncwarp();
+        if (!resolved && (rel & 3) == 0) xw_resolve(c, p, rel + 4);
+        if (rel + 1 < p.ev_count) xw_prepare<TW>(p, base, gi, lane, b, (int)(rel + 1), kind);
+      }
+      if (stage) c.evb[32 * (int)((rel + 2) & (EVSLOTS - 1)) + lane] = ev_next;
+      PH(c, 16 + kind)
+      if (FPC > 1 && ((int)rel & (LOCKSTEP - 1)) == LOCKSTEP - 1)
+        __syncthreads();
+      else
+        c.sync();
+      PH(c, 16 + kind + 32)
+    }
+    c.sync();
+    if (!active) continue;
+    latch_nan_state(c, tile_nan_scan<TW, false>(c, Pz));  // NaNsInTheHouse at the end of the slice (with the P warps)
   }
-};
+}
 
 // ------------------------------------------------------------------------------------------------------------------
 // the persistent tape executor, register-tile variant: a group of 32 (TW + 1) threads per filter, FPC groups per CTA.
@@ -1029,56 +1395,46 @@ struct TileCore {
 // instructions at any time (the executor is instruction-fetch bound when its CTAs drift apart over the ~0.5 MB of code).
 // ------------------------------------------------------------------------------------------------------------------
 template <int TW, int FPC>
-__global__ void __launch_bounds__(32 * (TW + 1) * FPC, (32 * (TW + 1) * FPC <= 128 ? 4 : (32 * (TW + 1) * FPC <= 256 ? 2 : 1))) viekf_tile_kernel(const __grid_constant__ KParams p) {
+__global__ void __launch_bounds__(32 * (TW + 1) * FPC, (384 / (32 * (TW + 1) * FPC) >= 1 ? 384 / (32 * (TW + 1) * FPC) : 1))
+    viekf_tile_kernel(const __grid_constant__ KParams p) {
   extern __shared__ __align__(16) double smem[];
   constexpr int G = 32 * (TW + 1);
-  const TLayout L = make_tlayout(p.N);
+  constexpr int PTH = 32 * TW;
+  constexpr TLayout L = make_tlayout(tile_cap<TW>());
+  const int gi = threadIdx.x / G;
+  // warp w of the CTA issues on SM sub-partition w % 4: when G is a multiple of 128 the x warps of all filters of the CTA would
+  // share one sub-partition; rotating the roles by the filter index spreads them
+  const int tid = (G % 128 == 0) ? (int)((threadIdx.x % G) + 32 * gi) % G : (int)(threadIdx.x % G);
+  double* base = smem + gi * L.total;
+  if ((tid >> 5) == TW) {
+    x_role<TW, FPC>(p, base, gi, tid & 31);
+    return;
+  }
+  // ---- the P role ----
   TCtx<TW> c;
-  c.gi = threadIdx.x / G;
-#ifdef VIEKF_ROLE_ROTATE
-  // warp w of the CTA issues on SM sub-partition w % 4: with G = 128 the base warps of all filters of a CTA would share one
-  // sub-partition (and its 16 FP64 lanes); rotating the roles by the filter index spreads them
-  c.tid = (int)((threadIdx.x % G) + 32 * c.gi) % G;
-#else
-  c.tid = threadIdx.x % G;
-#endif
-  c.lane = c.tid & 31;
-  c.basew = (c.tid >> 5) == TW;
+  init_tctx(c, base);
+  c.gi = gi;
+  c.tid = tid;
+  c.lane = tid & 31;
+  c.xw = false;
   {
-    const int t = c.tid;
+    const int t = tid;
     int ti = (int)((sqrtf(8.0f * (float)t + 1.0f) - 1.0f) * 0.5f);
     while (((ti + 1) * (ti + 2) >> 1) <= t) ti++;
     while (((ti * (ti + 1)) >> 1) > t) ti--;
     c.ti = ti;
     c.tj = t - ((ti * (ti + 1)) >> 1);
-    c.tile = !c.basew && ti < L.TR;
+    c.tile = ti < L.TR;
   }
-  double* base = smem + (size_t)c.gi * L.total;
-  c.x = base + L.x; c.P = base + L.T; c.lam = base + L.lam; c.dx = base + L.dx; c.Abd = base + L.Abd; c.AbT = base + L.AbT; c.T = base + L.T;
-  c.Ac = base + L.Ac; c.Gb = base + L.Gb; c.Afd = base + L.Afd; c.Gd = base + L.Gd; c.Y = base + L.Y; c.upd = base + L.upd;
-  c.Pbb = base + L.Pbb; c.Pfb = base + L.Pfb;
-  c.sm = base + L.small;
-  c.ids = (int*)(base + L.ids);
-  c.rm = c.ids + p.N;
-  c.sc = c.rm + p.N;
-  c.smap = (int*)(base + L.smap);
-  c.fixk = (int*)(base + L.fixk);
-  c.fixv = base + L.fixv;
-  c.zvr = base + L.zvr;
-  c.tcur = c.sm + SM_T;
-  double* evb = base + L.evb;
-  constexpr int EVW = (int)(sizeof(viekf_event) / sizeof(double));
-  static_assert(sizeof(viekf_event) % sizeof(double) == 0 && EVW <= 32, "viekf_event must fit one warp of doubles");
-  constexpr int EVT0 = (G >= 96) ? 64 : 32;  // first thread of the warp that stages the next event record (warp 2; the base warp when TW = 1)
-  const int nmaxp = 16 + 6 * L.TR;
-  for (int i = c.tid; i < nmaxp; i += G) c.lam[i] = (i < 16) ? p.lam[i] : p.lamf[(i - 16) % 3];
-  for (int i = c.tid; i < 2 * L.TR; i += G) c.fixk[i] = 0;
+  constexpr int nmaxp = 16 + 6 * L.TR;
+  for (int i = tid; i < nmaxp; i += PTH) c.lam[i] = (i < 16) ? p.lam[i] : p.lamf[(i - 16) % 3];
+  for (int i = tid; i < 2 * L.TR; i += PTH) c.fixk[i] = 0;
   double Pt[36];
   PH_INIT(c)
 
   for (int64_t b0 = (int64_t)blockIdx.x * FPC; b0 < p.B; b0 += (int64_t)gridDim.x * FPC) {
-    const bool active = b0 + c.gi < p.B;  // a group without a filter still takes part in the CTA-wide event barriers
-    const int64_t b = active ? b0 + c.gi : 0;
+    const bool active = b0 + gi < p.B;  // a group without a filter still takes part in the CTA-wide event barriers
+    const int64_t b = active ? b0 + gi : 0;
     c.b = b;
     const int64_t ginst = p.inst_off + b;
     c.ginst = ginst;
@@ -1087,113 +1443,97 @@ __global__ void __launch_bounds__(32 * (TW + 1) * FPC, (32 * (TW + 1) * FPC <= 1
     // ---- load the filter: meta, ids, live part of x; P_bb / P_fb into shared memory, P_ff into the register tiles ----
     c.sync();
     const int len0 = M.len;
-    if (c.tid == 0) {
+    if (tid == 0) {
       c.sc[SC_LEN] = len0; c.sc[SC_NEXT] = M.next_id; c.sc[SC_STARTED] = M.started; c.sc[SC_FLAGS] = (int)M.flags;
       c.sc[SC_NGATED] = (int)M.n_gated; c.sc[SC_NFIX] = (int)M.n_fix; c.sc[SC_NNAN] = (int)M.n_nan_gain; c.sc[SC_NKF] = M.n_kf;
       *c.tcur = M.t;
       for (int k = 0; k < 6; k++) c.sm[SM_UB + k] = M.ub[k];
     }
-    for (int i = c.tid; i < len0; i += G) c.ids[i] = p.ids[b * (p.N > 0 ? p.N : 1) + i];
+    for (int i = tid; i < len0; i += PTH) c.ids[i] = p.ids[b * (p.N > 0 ? p.N : 1) + i];
     {
       const double* gx = p.x + b * p.xs;
       const int nx = 17 + 5 * len0;
-      for (int i = c.tid; i < nx; i += G) c.x[i] = gx[i];
-      for (int e = c.tid; e < 256; e += G) {
+      for (int i = tid; i < nx; i += PTH) c.x[i] = gx[i];
+      for (int e = tid; e < 256; e += PTH) {
         const int r = e >> 4, cc = e & 15;
         c.Pbb[r * PBS + cc] = gP[psym(r, cc)];
       }
       const int nfr0 = 3 * ((len0 + 1) & ~1);
-      for (int e = c.tid; e < nfr0 * 16; e += G) {
+      for (int e = tid; e < nfr0 * 16; e += PTH) {
         const int fr = e >> 4, cc = e & 15;
         c.Pfb[fr * 17 + cc] = (fr < 3 * len0) ? gP[plo(16 + fr, cc)] : 0.0;
       }
       tile_load(c, gP, Pt, len0, false);
     }
-    if (p.ev_count > 0 && c.tid < 8) resolve_values(p, p.ev_first, b, ginst, c.tid, c.zvr);
-    if (p.ev_count > 0 && c.tid >= EVT0 && c.tid < EVT0 + EVW) evb[c.tid - EVT0] = ((const double*)(p.ev + p.ev_first))[c.tid - EVT0];
     PHS(c, 0)
+    c.sync();  // the x warp has prepared the first event
     // ---- run the tape slice ----
-    for (int64_t e = p.ev_first; e < p.ev_first + p.ev_count; e++) {
-      // the event record is read from shared memory; the next one is fetched now (one double per lane of warp 2) and
-      // staged just before the barrier that ends this event
-      const viekf_event& E = *(const viekf_event*)(evb + 32 * (int)((e - p.ev_first) & 1));
+    for (int64_t rel = 0; rel < p.ev_count; rel++) {
+      const int64_t e = p.ev_first + rel;
+      // the event record and its prepared model are read from shared memory (staged / written by the x warp)
+      const viekf_event& E = *(const viekf_event*)(c.evb + 32 * (int)(rel & (EVSLOTS - 1)));
+      const double* Mod = c.model + MD_SIZE * (int)(rel & 1);
       tile_apply_fix(c, p, Pt);  // depth corrections recorded by the previous event
-      double ev_next = 0.0;
-      const bool stage = (e + 1 < p.ev_first + p.ev_count) && c.tid >= EVT0 && c.tid < EVT0 + EVW;
-      if (stage) ev_next = __ldg((const double*)(p.ev + e + 1) + (c.tid - EVT0));
       const int kind = E.kind;
-      c.zv = c.zvr + 8 * (int)((e - p.ev_first) & 7);
-      c.next_e = (((e - p.ev_first) & 3) == 0 && e + 1 < p.ev_first + p.ev_count) ? e + 1 : -1;
-      c.resolved = false;
+      c.zv = c.zvr + 8 * (int)(rel & 7);
       int result = VIEKF_MEAS_NONE;
       if (active) {
-      if (kind != VIEKF_EV_PROP && kind != VIEKF_EV_UPD) resolve_next(c, p, 32);
-      switch (kind) {
-        case VIEKF_EV_PROP:
-          tile_propagate(c, p, E, Pt);
-          break;
-        case VIEKF_EV_UPD: {
-          TileCore<TW> core{c, p, Pt};
-          result = ev_update(c, p, E, core);
-          break;
+        if (kind == VIEKF_EV_PROP) {
+          p_propagate(c, p, Mod, Pt);
+        } else if (kind == VIEKF_EV_UPD) {
+          const int mk = ((const int*)(Mod + MD_INT))[MI_KIND];
+          if (mk == MK_NAN) {
+            result = VIEKF_MEAS_NAN;
+          } else if (mk == MK_INVALID) {
+            result = VIEKF_MEAS_INVALID;  // the reference would index the state with -1 here (UB)
+          } else if (mk == MK_NEWFEAT) {
+            tile_init_feature<TW, true>(c, p, c.zv[0], c.zv[1], E.z[4], Pt);
+            result = VIEKF_MEAS_NEW_FEATURE;
+          } else if (mk == MK_INACTIVE) {
+            result = VIEKF_MEAS_SUCCESS;  // logged only: the x warp runs fix_depth (vi_ekf_meas.cpp:230,271)
+          } else {
+            const int rd = E.rdim;  // one call site per residual dimension
+            if (rd == 1) result = p_update<TW, 1>(c, p, Mod, Pt);
+            else if (rd == 2) result = p_update<TW, 2>(c, p, Mod, Pt);
+            else result = p_update<TW, 3>(c, p, Mod, Pt);
+          }
+        } else {
+          result = generic_event<TW, true>(c, p, E, kind, ginst, Pt);
         }
-        case VIEKF_EV_INIT:
-          result = tile_init_feature(c, p, c.zv[0], c.zv[1], E.z[4], Pt) ? 1 : 0;
-          break;
-        case VIEKF_EV_CLEAR:
-          tile_clear_feature(c, p, find_feature(c, E.id), Pt);
-          break;
-        case VIEKF_EV_KEEP:
-          tile_keep_only(c, p, p.id_pool + E.ids_off, E.n_ids, Pt);
-          break;
-        case VIEKF_EV_KFRESET:
-          tile_keyframe_reset(c, p);
-          break;
-        case VIEKF_EV_STAT:
-          c.sync();
-          tile_pack_base(c);
-          c.sync();
-          ev_stat(c, p, E, ginst, [&]() { return tile_nan_scan(c, Pt); });
-          break;
-        default:
-          break;
       }
-      if (!c.resolved) resolve_next(c, p, 32);  // the handler returned before its deferred slot (uniform)
-      }
-      if (stage) evb[32 * (int)((e + 1 - p.ev_first) & 1) + (c.tid - EVT0)] = ev_next;
       PH(c, 16 + kind)
       // the filters of a CTA re-align every LOCKSTEP events (all start the next event together); in between only the group
       // synchronises, so a filter that finishes an event early (gated update, fewer live features) is not held back each time
-      if (FPC > 1 && ((int)(e - p.ev_first) & (LOCKSTEP - 1)) == LOCKSTEP - 1)
+      if (FPC > 1 && ((int)rel & (LOCKSTEP - 1)) == LOCKSTEP - 1)
         __syncthreads();
       else
         c.sync();
       PH(c, 16 + kind + 32)
-      if (p.results && active && c.tid == 0 && b >= p.res_first && b < p.res_first + p.res_count)
+      if (p.results && active && tid == 0 && b >= p.res_first && b < p.res_first + p.res_count)
         p.results[(b - p.res_first) * p.n_events + e] = (uint8_t)result;
     }
     // ---- store the filter ----
     c.sync();
     if (!active) continue;
     tile_apply_fix(c, p, Pt);
-    latch_nan_state(c, tile_nan_scan(c, Pt));  // NaNsInTheHouse at the end of the slice
+    latch_nan_state(c, tile_nan_scan<TW, true>(c, Pt));  // NaNsInTheHouse at the end of the slice
     const int len1 = c.sc[SC_LEN];
-    if (c.tid == 0) {
+    if (tid == 0) {
       M.len = len1; M.next_id = c.sc[SC_NEXT]; M.started = c.sc[SC_STARTED]; M.flags = (uint32_t)c.sc[SC_FLAGS];
       M.n_gated = (uint32_t)c.sc[SC_NGATED]; M.n_fix = (uint32_t)c.sc[SC_NFIX]; M.n_nan_gain = (uint32_t)c.sc[SC_NNAN]; M.n_kf = c.sc[SC_NKF];
       M.t = *c.tcur;
       for (int k = 0; k < 6; k++) M.ub[k] = c.sm[SM_UB + k];
     }
-    for (int i = c.tid; i < len1; i += G) p.ids[b * (p.N > 0 ? p.N : 1) + i] = c.ids[i];
+    for (int i = tid; i < len1; i += PTH) p.ids[b * (p.N > 0 ? p.N : 1) + i] = c.ids[i];
     {
       double* gx = p.x + b * p.xs;
       const int nx = 17 + 5 * len1;
-      for (int i = c.tid; i < nx; i += G) gx[i] = c.x[i];
-      for (int e = c.tid; e < 256; e += G) {
+      for (int i = tid; i < nx; i += PTH) gx[i] = c.x[i];
+      for (int e = tid; e < 256; e += PTH) {
         const int r = e >> 4, cc = e & 15;
         if (cc <= r) gP[plo(r, cc)] = c.Pbb[r * PBS + cc];
       }
-      for (int e = c.tid; e < 3 * len1 * 16; e += G) {
+      for (int e = tid; e < 3 * len1 * 16; e += PTH) {
         const int fr = e >> 4, cc = e & 15;
         gP[plo(16 + fr, cc)] = c.Pfb[fr * 17 + cc];
       }
@@ -1209,7 +1549,7 @@ extern "C" int viekf_debug_phase_clocks(unsigned long long* clk, unsigned long l
   cudaMemcpyFromSymbol(clk, g_phase_clk, sizeof(g_phase_clk));
   cudaMemcpyFromSymbol(cnt, g_phase_cnt, sizeof(g_phase_cnt));
   if (reset) {
-    static unsigned long long z[4 * 64];
+    static unsigned long long z[8 * 64];
     cudaMemcpyToSymbol(g_phase_clk, z, sizeof(z));
     cudaMemcpyToSymbol(g_phase_cnt, z, sizeof(z));
   }
@@ -1257,23 +1597,22 @@ static cudaError_t launch_tile_fpc(const KParams& p, int sm_count, cudaStream_t 
 cudaError_t launch_tile(const KParams& p, int sm_count, cudaStream_t stream) {
   const int tw = tile_warps_for(p.N);
   if (tw == 0) return cudaErrorInvalidValue;
-  // filters per CTA in event lock-step.  TW = 3: 3 (384 threads, 168 registers each: the 72-register tile plus a schedule with
-  // loads in flight; 4 x 128 registers spills on the hot path).  TW = 6: 2 (448 threads, 144 registers).  Small batches spread
-  // over the SMs first.
-  // TW = 1 (N <= 14, config #3 at N = 8): 6 filters of 64 threads per CTA.
+  // filters per CTA in event lock-step: 384 threads (168 registers each) per CTA wherever the shared memory allows --
+  // TW = 1 (N <= 14, config #3 at N = 8): 6 filters of 64 threads; TW = 3 (N <= 26, config #4): 3 filters of 128 threads;
+  // TW = 6 (N <= 36, config #5): 2 filters of 224 threads (144 registers).  Small batches spread over the SMs first.
   const int full = (tw == 1) ? 6 : ((tw == 3) ? 3 : 2);
   int fpc = (p.B < full * (int64_t)sm_count) ? 1 : full;
   if (const char* s = getenv("VIEKF_TILE_FPC")) fpc = atoi(s);  // test / tuning override; a value without an instantiation is an error
 #ifdef VIEKF_DEV_FAST  // development build: only the configs[3] instantiations (each one costs ~25 s of ptxas)
   if (tw == 3 && fpc == 1) return launch_tile_fpc<3, 1>(p, sm_count, stream);
   if (tw == 3 && fpc == 3) return launch_tile_fpc<3, 3>(p, sm_count, stream);
+  if (tw == 3 && fpc == 2) return launch_tile_fpc<3, 2>(p, sm_count, stream);
   return cudaErrorInvalidValue;
 #else
   if (tw == 1) {
     switch (fpc) {
       case 1: return launch_tile_fpc<1, 1>(p, sm_count, stream);
       case 2: return launch_tile_fpc<1, 2>(p, sm_count, stream);
-      case 4: return launch_tile_fpc<1, 4>(p, sm_count, stream);
       case 6: return launch_tile_fpc<1, 6>(p, sm_count, stream);
       default: return cudaErrorInvalidValue;
     }
@@ -1283,7 +1622,6 @@ cudaError_t launch_tile(const KParams& p, int sm_count, cudaStream_t stream) {
       case 1: return launch_tile_fpc<3, 1>(p, sm_count, stream);
       case 2: return launch_tile_fpc<3, 2>(p, sm_count, stream);
       case 3: return launch_tile_fpc<3, 3>(p, sm_count, stream);
-      case 4: return launch_tile_fpc<3, 4>(p, sm_count, stream);
       default: return cudaErrorInvalidValue;
     }
   }
