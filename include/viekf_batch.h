@@ -85,6 +85,12 @@ typedef struct viekf_config {
 
 /* Fills cfg with the values of the reference's params/ekf.yaml. */
 void viekf_config_default(viekf_config* cfg);
+/* VIEKF(param_file) / load (vi_ekf.cpp:101-155): starts from viekf_config_default and overrides every key of the YAML file
+ * that load() reads (x0, P0, P0_feat, Qx, Qx_feat, Qu, lambda, lambda_feat, cam_center, focal_len, q_b_c, p_b_c, q_b_u,
+ * min_depth, keyframe_overlap_threshold, use_drag_term, use_partial_update, use_keyframe_reset).  Flat `key: value` /
+ * `key: [v, v, ...]` YAML (lists may span lines, `#` comments), which is all params/ekf.yaml uses.  VIEKF_ERR_ARG on an
+ * unreadable file or a list of the wrong length. */
+int viekf_config_load_yaml(const char* path, viekf_config* cfg);
 
 /* ---- in-order event tape (replaces the rewind/replay queue, vi_ekf_meas.cpp:6-194) --- */
 typedef enum {
@@ -175,6 +181,22 @@ int viekf_batch_get_flags(viekf_batch* h, int64_t first, int64_t count, uint32_t
 /* get_global_pose / global_pose_cov_ bookkeeping of keyframe_reset (vi_ekf_kfr.cpp:14-55): node pose [t(3), q(4)] x count
  * and the accumulated 6x6 global covariance (column-major, may be NULL). */
 int viekf_batch_get_global_pose(viekf_batch* h, int64_t first, int64_t count, double* node_t3q4, double* gcov36);
+/* get_covariance_diagonal (vi_ekf.cpp:202-206): d is [MAX_DX x count]; entries beyond the live 16 + 3 len are 0. */
+int viekf_batch_get_covariance_diagonal(viekf_batch* h, int64_t first, int64_t count, double* d);
+/* get_depths / get_zetas / get_qzetas (vi_ekf.cpp:210-240): depths [N x count] = 1 / rho, zetas [3 x N x count] = q_zeta.rota(e_z),
+ * qzetas [4 x N x count]; entries of feature slots beyond len_features are NaN (the reference returns len_features columns). */
+int viekf_batch_get_depths(viekf_batch* h, int64_t first, int64_t count, double* depths);
+int viekf_batch_get_zetas(viekf_batch* h, int64_t first, int64_t count, double* zetas);
+int viekf_batch_get_qzetas(viekf_batch* h, int64_t first, int64_t count, double* qzetas);
+/* get_depth(id) / get_feat(id) (vi_ekf.cpp:242-260): depth[count], pixel[2 x count] of the feature with that (internal) id;
+ * NaN for an instance that does not track it (the reference indexes the state with -1 there). get_zeta(i) is column i of
+ * viekf_batch_get_zetas. */
+int viekf_batch_get_depth(viekf_batch* h, int32_t id, int64_t first, int64_t count, double* depth);
+int viekf_batch_get_feat(viekf_batch* h, int32_t id, int64_t first, int64_t count, double* pixel);
+/* set_imu_bias(b_g, b_a) (vi_ekf.cpp:180-184) on every instance; set_drag_term / get_drag_term (include/vi_ekf.h:291-292). */
+int viekf_batch_set_imu_bias(viekf_batch* h, const double* b_g, const double* b_a);
+int viekf_batch_set_drag_term(viekf_batch* h, int32_t use_drag_term);
+int viekf_batch_get_drag_term(const viekf_batch* h);
 /* current filter time t_[i_] of each instance */
 int viekf_batch_get_time(viekf_batch* h, int64_t first, int64_t count, double* t);
 

@@ -18,6 +18,7 @@
 #include <cstdint>
 #include <stdexcept>
 #include <string>
+#include <array>
 #include <vector>
 #include "viekf_batch.h"
 #if defined(__has_include)
@@ -134,6 +135,50 @@ class BatchVIEKF {
     return std::vector<int>(ids.begin(), ids.begin() + len);
   }
   int get_len_features(int64_t instance = 0) { return (int)tracked_features(instance).size(); }
+  // vi_ekf.cpp:202-260 (feature slots beyond len_features are NaN; an untracked id gives NaN)
+  std::vector<double> get_covariance_diagonal(int64_t first = 0, int64_t count = -1) {
+    if (count < 0) count = B_ - first;
+    std::vector<double> d((size_t)(count * max_dx()));
+    check(viekf_batch_get_covariance_diagonal(h_, first, count, d.data()));
+    return d;
+  }
+  std::vector<double> get_depths(int64_t first = 0, int64_t count = -1) {
+    if (count < 0) count = B_ - first;
+    std::vector<double> d((size_t)(count * (N_ > 0 ? N_ : 1)), NAN);
+    check(viekf_batch_get_depths(h_, first, count, d.data()));
+    return d;
+  }
+  std::vector<double> get_zetas(int64_t first = 0, int64_t count = -1) {
+    if (count < 0) count = B_ - first;
+    std::vector<double> z((size_t)(3 * count * (N_ > 0 ? N_ : 1)), NAN);
+    check(viekf_batch_get_zetas(h_, first, count, z.data()));
+    return z;
+  }
+  std::vector<double> get_qzetas(int64_t first = 0, int64_t count = -1) {
+    if (count < 0) count = B_ - first;
+    std::vector<double> q((size_t)(4 * count * (N_ > 0 ? N_ : 1)), NAN);
+    check(viekf_batch_get_qzetas(h_, first, count, q.data()));
+    return q;
+  }
+  double get_depth(int id, int64_t instance = 0) {
+    double d = NAN;
+    check(viekf_batch_get_depth(h_, id, instance, 1, &d));
+    return d;
+  }
+  std::array<double, 2> get_feat(int id, int64_t instance = 0) {
+    std::array<double, 2> px{NAN, NAN};
+    check(viekf_batch_get_feat(h_, id, instance, 1, px.data()));
+    return px;
+  }
+  void set_imu_bias(const double (&b_g)[3], const double (&b_a)[3]) { check(viekf_batch_set_imu_bias(h_, b_g, b_a)); }
+  void set_drag_term(bool use_drag_term) { check(viekf_batch_set_drag_term(h_, use_drag_term ? 1 : 0)); }
+  bool get_drag_term() const { return viekf_batch_get_drag_term(h_) != 0; }
+  // VIEKF(param_file) (vi_ekf.cpp:101-155)
+  static viekf_config load(const std::string& param_file) {
+    viekf_config c;
+    check(viekf_config_load_yaml(param_file.c_str(), &c));
+    return c;
+  }
   double get_time(int64_t instance = 0) {
     double t = 0;
     check(viekf_batch_get_time(h_, instance, 1, &t));

@@ -58,3 +58,18 @@ def test_tape_builder_roundtrip(pkg):
     assert ev[1]["zdim"] == 2 and ev[1]["rdim"] == 2 and ev[1]["z"][4] == 2.5 and list(ev[1]["R"][:4]) == [3.0, 0.0, 0.0, 4.0]
     assert ev[2]["n_ids"] == 3 and list(tb.id_pool()) == [4, 5, 6]
     assert tb.n_imu_steps() == 1
+
+
+def test_config_load_yaml(lib, pkg):
+    """VIEKF(param_file) / load (reference vi_ekf.cpp:101-155): the C++ reader of params/ekf.yaml-style files."""
+    data = os.path.join(ROOT, "tests", "data")
+    c = pkg.abi.load_config(os.path.join(data, "ekf_default.yaml"))
+    assert bytes(c) == bytes(pkg.abi.default_config()), "the fixture carries the defaults: the loaded configuration must equal viekf_config_default"
+    o = pkg.abi.load_config(os.path.join(data, "ekf_override.yaml"))
+    assert list(o.Qu) == [2.0, 2.0, 2.0, 1e-3, 1e-3, 1e-3] and o.use_drag_term == 0 and o.use_keyframe_reset == 0 and o.use_partial_update == 1
+    assert o.min_depth == 0.75 and list(o.lambda_feat) == [0.5, 0.5, 0.25] and list(o.P0) == list(c.P0)
+    with pytest.raises(RuntimeError) as e:
+        pkg.abi.load_config(os.path.join(data, "ekf_bad.yaml"))
+    assert "P0_feat" in str(e.value)
+    with pytest.raises(RuntimeError):
+        pkg.abi.load_config(os.path.join(data, "does_not_exist.yaml"))

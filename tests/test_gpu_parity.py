@@ -367,3 +367,55 @@ def test_baseline_sizes_properties(pkg, oracle_mod, B, NF, steps):
         d = np.diag(P)[: 16 + 3 * ln[b]]
         assert (d >= 0).all() and (d[3:] > 0).all()  # the position block is exactly zero right after a keyframe reset
         tapes.live_compare(x, P, ln[b], ref["x"][0], ref["P"][0], ref["len"][0], REL_TOL, f"B={B} inst {b}")
+
+
+def test_read_back_getters(pkg, oracle_mod):
+    """get_depths / get_zetas / get_qzetas / get_zeta / get_feat / get_depth / get_covariance_diagonal, set_imu_bias, set_drag_term
+    (reference include/vi_ekf.h:276-292, src/vi_ekf/vi_ekf.cpp:180-260) against the oracle's state after a tape."""
+    from oracle import np_oracle
+    cfg = _default_cfg()
+    NF, B = 6, 3
+    ev, idp, f, nb = tapes.consistent_tape(oracle_mod, cfg, NF, steps=30, seed=9, extra_models=False)
+    bk = pkg.BatchVIEKF(cfg, B=B, N=NF)
+    bk.run_tape(ev, idp)
+    x, P = f.get_state(), f.get_covariance()
+    ln = f.get_len_features()
+    ids = f.tracked_features()
+    assert 0 < ln <= NF
+    dep, zet, qz = bk.get_depths(), bk.get_zetas(), bk.get_qzetas()
+    dg = bk.get_covariance_diagonal()
+    for b in range(B):
+        for i in range(NF):
+            if i < ln:
+                q = x[17 + 5 * i:17 + 5 * i + 4]
+                assert np.allclose(dep[b, i], 1.0 / x[17 + 5 * i + 4], rtol=1e-9)
+                assert np.allclose(qz[b, i], q, rtol=1e-9, atol=1e-12)
+                assert np.allclose(zet[b, i], np_oracle.zeta_of(q), rtol=1e-9, atol=1e-12)
+            else:
+                assert np.isnan(dep[b, i]) and np.isnan(zet[b, i]).all() and np.isnan(qz[b, i]).all()
+        n = 16 + 3 * ln
+        assert np.allclose(dg[b, :n], np.diag(P)[:n], rtol=1e-9, atol=1e-15) and (dg[b, n:] == 0).all()
+    assert np.array_equal(bk.get_zeta(0), zet[:, 0])
+    fid = ids[-1]
+    zh, _ = f.h_model(abi.FEAT, x, fid)
+    assert np.allclose(bk.get_feat(fid), np.tile(zh[:2], (B, 1)), rtol=1e-9)
+    assert np.allclose(bk.get_depth(fid), 1.0 / x[17 + 5 * (ln - 1) + 4], rtol=1e-9)
+    assert np.isnan(bk.get_depth(123456)).all() and np.isnan(bk.get_feat(123456)).all()
+    # set_imu_bias / set_drag_term
+    bk.set_imu_bias([0.01, 0.02, 0.03], [0.1, 0.2, 0.3])
+    xs = bk.get_state()
+    assert np.array_equal(xs[:, 13:16], np.tile([0.01, 0.02, 0.03], (B, 1))) and np.array_equal(xs[:, 10:13], np.tile([0.1, 0.2, 0.3], (B, 1)))
+    assert bk.get_drag_term() is True
+    bk.set_drag_term(False)
+    assert bk.get_drag_term() is False
+    cfg2 = _default_cfg(use_drag_term=0)
+    # a no-drag propagate from the same state: the handle now follows the no-drag dynamics (vi_ekf_dyn.cpp:44-49)
+    t0 = bk.get_time(0, 1)[0]
+    u = tapes.imu_at(t0 + 0.005)
+    bk.propagate_state(u, t0 + 0.005)
+    x1 = bk.get_state()[0]
+    g2 = np_oracle.NpVIEKF(cfg2, NF)
+    g2.x, g2.P = xs[0].copy(), bk.get_covariance()[0].copy()
+    g2.len, g2.ids, g2.started, g2.t = ln, list(ids), True, t0
+    g2.propagate_state(u, t0 + 0.005)
+    assert np.allclose(x1[:17 + 5 * ln], g2.x[:17 + 5 * ln], rtol=1e-9, atol=1e-12)

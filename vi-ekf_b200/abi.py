@@ -69,6 +69,16 @@ def default_config():
     return c
 
 
+def load_config(path):
+    """VIEKF(param_file) / load (reference vi_ekf.cpp:101-155): the configuration of a params/ekf.yaml-style file."""
+    L = load_library()
+    c = Config()
+    rc = L.viekf_config_load_yaml(str(path).encode(), C.byref(c))
+    if rc != 0:
+        raise RuntimeError(f"viekf_config_load_yaml({path}): {rc}: {L.viekf_last_error().decode()}")
+    return c
+
+
 # numpy mirror of viekf_event (248 bytes)
 EVENT_DTYPE = np.dtype([
     ("kind", "<i4"), ("type", "<i4"), ("id", "<i4"), ("active", "<i4"), ("zdim", "<i4"), ("rdim", "<i4"),
@@ -116,6 +126,16 @@ def load_library():
         "viekf_batch_get_flags": (i32, [vp, i64, i64, vp, vp]),
         "viekf_batch_get_time": (i32, [vp, i64, i64, vp]),
         "viekf_batch_get_global_pose": (i32, [vp, i64, i64, vp, vp]),
+        "viekf_batch_get_covariance_diagonal": (i32, [vp, i64, i64, vp]),
+        "viekf_batch_get_depths": (i32, [vp, i64, i64, vp]),
+        "viekf_batch_get_zetas": (i32, [vp, i64, i64, vp]),
+        "viekf_batch_get_qzetas": (i32, [vp, i64, i64, vp]),
+        "viekf_batch_get_depth": (i32, [vp, i32, i64, i64, vp]),
+        "viekf_batch_get_feat": (i32, [vp, i32, i64, i64, vp]),
+        "viekf_batch_set_imu_bias": (i32, [vp, vp, vp]),
+        "viekf_batch_set_drag_term": (i32, [vp, i32]),
+        "viekf_batch_get_drag_term": (i32, [vp]),
+        "viekf_config_load_yaml": (i32, [C.c_char_p, C.POINTER(Config)]),
         "viekf_batch_set_instance_offset": (i32, [vp, i64]),
         "viekf_fp64_peak_probe": (i32, [i32, pd]),
         "viekf_batch_propagate": (i32, [vp, vp, i32, dbl]),

@@ -89,6 +89,59 @@ class BatchVIEKF:
         self._chk(self.L.viekf_batch_get_global_pose(self.h, first, count, _p(pose), _p(cov)))
         return pose, cov.transpose(0, 2, 1)
 
+    # ---- feature / covariance read-back (reference vi_ekf.cpp:202-260) ------------------------------------
+    def get_covariance_diagonal(self, first=0, count=None):
+        count = self.B - first if count is None else count
+        d = np.zeros((count, self.MAX_DX))
+        self._chk(self.L.viekf_batch_get_covariance_diagonal(self.h, first, count, _p(d)))
+        return d
+
+    def get_depths(self, first=0, count=None):
+        """1 / rho per feature slot, NaN beyond len_features."""
+        count = self.B - first if count is None else count
+        d = np.full((count, max(self.N, 1)), np.nan)
+        self._chk(self.L.viekf_batch_get_depths(self.h, first, count, _p(d)))
+        return d[:, : self.N]
+
+    def get_zetas(self, first=0, count=None):
+        count = self.B - first if count is None else count
+        z = np.full((count, max(self.N, 1), 3), np.nan)
+        self._chk(self.L.viekf_batch_get_zetas(self.h, first, count, _p(z)))
+        return z[:, : self.N]
+
+    def get_qzetas(self, first=0, count=None):
+        count = self.B - first if count is None else count
+        q = np.full((count, max(self.N, 1), 4), np.nan)
+        self._chk(self.L.viekf_batch_get_qzetas(self.h, first, count, _p(q)))
+        return q[:, : self.N]
+
+    def get_zeta(self, i, first=0, count=None):
+        return self.get_zetas(first, count)[:, i]
+
+    def get_depth(self, id, first=0, count=None):
+        count = self.B - first if count is None else count
+        d = np.zeros(count)
+        self._chk(self.L.viekf_batch_get_depth(self.h, int(id), first, count, _p(d)))
+        return d
+
+    def get_feat(self, id, first=0, count=None):
+        count = self.B - first if count is None else count
+        px = np.zeros((count, 2))
+        self._chk(self.L.viekf_batch_get_feat(self.h, int(id), first, count, _p(px)))
+        return px
+
+    def set_imu_bias(self, b_g, b_a):
+        bg = np.ascontiguousarray(b_g, dtype=np.float64)
+        ba = np.ascontiguousarray(b_a, dtype=np.float64)
+        assert bg.shape == (3,) and ba.shape == (3,)
+        self._chk(self.L.viekf_batch_set_imu_bias(self.h, _p(bg), _p(ba)))
+
+    def set_drag_term(self, use_drag_term):
+        self._chk(self.L.viekf_batch_set_drag_term(self.h, int(bool(use_drag_term))))
+
+    def get_drag_term(self):
+        return bool(self.L.viekf_batch_get_drag_term(self.h))
+
     def set_instance_offset(self, first_global_instance):
         self._chk(self.L.viekf_batch_set_instance_offset(self.h, int(first_global_instance)))
 

@@ -65,7 +65,31 @@ struct viekf_batch {
   int32_t* d_ids = nullptr;   // [KF_CAP]
   uint8_t* d_res = nullptr;   // [B]
   double* d_x0 = nullptr;     // [B][17]
+  // grow-only device staging owned by the handle (read-back unpack buffers, per-event results, the tape of run_tape): no
+  // cudaMalloc / cudaFree on the per-call paths once they are warm
+  void* d_stage = nullptr;
+  size_t stage_cap = 0;
+  void* d_res_stage = nullptr;
+  size_t res_cap = 0;
+  viekf_event* d_tape_ev = nullptr;
+  size_t tape_ev_cap = 0;  // events
+  int32_t* d_tape_ids = nullptr;
+  size_t tape_ids_cap = 0;  // ids
+  double* d_tape_vals = nullptr;
+  size_t tape_vals_cap = 0;  // doubles
 };
+
+// grow-only allocation: *buf holds at least `need` bytes afterwards
+static cudaError_t grow(void** buf, size_t* cap, size_t need) {
+  if (need <= *cap) return cudaSuccess;
+  cudaFree(*buf);
+  *buf = nullptr;
+  *cap = 0;
+  const size_t want = need + need / 4;
+  cudaError_t e = cudaMalloc(buf, want);
+  if (e == cudaSuccess) *cap = want;
+  return e;
+}
 
 static int fail(int code, const char* what, cudaError_t e = cudaSuccess) {
   char buf[512];
@@ -160,6 +184,99 @@ void viekf_config_default(viekf_config* c) {
   c->use_keyframe_reset = 1;
 }
 
+// VIEKF::load (vi_ekf.cpp:101-155) for the flat YAML of params/ekf.yaml: `key: scalar` or `key: [v, v, ...]` (a list may span
+// lines), `#` starts a comment.
+static bool yaml_flat(const char* path, std::vector<std::pair<std::string, std::vector<std::string>>>& out) {
+  FILE* f = fopen(path, "r");
+  if (!f) return false;
+  std::string text;
+  char buf[4096];
+  size_t n;
+  while ((n = fread(buf, 1, sizeof(buf), f)) > 0) text.append(buf, n);
+  fclose(f);
+  std::string clean;  // comments removed
+  bool in_comment = false;
+  for (char ch : text) {
+    if (ch == '#') in_comment = true;
+    if (ch == '\n') in_comment = false;
+    if (!in_comment) clean.push_back(ch);
+  }
+  size_t pos = 0;
+  auto trim = [](std::string v) {
+    const size_t a = v.find_first_not_of(" \t\r\n\"'"), b = v.find_last_not_of(" \t\r\n\"'");
+    return a == std::string::npos ? std::string() : v.substr(a, b - a + 1);
+  };
+  while (pos < clean.size()) {
+    size_t eol = clean.find('\n', pos);
+    if (eol == std::string::npos) eol = clean.size();
+    std::string line = clean.substr(pos, eol - pos);
+    pos = eol + 1;
+    const size_t colon = line.find(':');
+    if (colon == std::string::npos) continue;
+    const std::string key = trim(line.substr(0, colon));
+    std::string val = line.substr(colon + 1);
+    if (key.empty()) continue;
+    std::vector<std::string> items;
+    const size_t lb = val.find('[');
+    if (lb != std::string::npos) {
+      while (val.find(']') == std::string::npos && pos < clean.size()) {  // the list continues on the next lines
+        size_t e2 = clean.find('\n', pos);
+        if (e2 == std::string::npos) e2 = clean.size();
+        val += " " + clean.substr(pos, e2 - pos);
+        pos = e2 + 1;
+      }
+      const size_t rb = val.find(']');
+      std::string body = val.substr(lb + 1, (rb == std::string::npos ? val.size() : rb) - lb - 1);
+      size_t p0 = 0;
+      while (p0 <= body.size()) {
+        size_t c = body.find(',', p0);
+        if (c == std::string::npos) c = body.size();
+        const std::string it = trim(body.substr(p0, c - p0));
+        if (!it.empty()) items.push_back(it);
+        p0 = c + 1;
+      }
+    } else {
+      const std::string it = trim(val);
+      if (!it.empty()) items.push_back(it);
+    }
+    out.push_back({key, items});
+  }
+  return true;
+}
+
+int viekf_config_load_yaml(const char* path, viekf_config* c) {
+  if (!path || !c) return fail(VIEKF_ERR_ARG, "viekf_config_load_yaml: null argument");
+  std::vector<std::pair<std::string, std::vector<std::string>>> kv;
+  if (!yaml_flat(path, kv)) return fail(VIEKF_ERR_ARG, "viekf_config_load_yaml: cannot read the file");
+  viekf_config_default(c);
+  struct Vec {
+    const char* key;
+    double* dst;
+    int n;
+  };
+  const Vec vecs[] = {{"x0", c->x0, 17}, {"P0", c->P0, 16}, {"P0_feat", c->P0_feat, 3}, {"Qx", c->Qx, 16}, {"Qx_feat", c->Qx_feat, 3},
+                      {"Qu", c->Qu, 6}, {"lambda", c->lambda, 16}, {"lambda_feat", c->lambda_feat, 3}, {"cam_center", c->cam_center, 2},
+                      {"focal_len", c->focal_len, 2}, {"q_b_c", c->q_b_c, 4}, {"p_b_c", c->p_b_c, 3}, {"q_b_u", c->q_b_u, 4},
+                      {"min_depth", &c->min_depth, 1}, {"keyframe_overlap_threshold", &c->keyframe_overlap_threshold, 1}};
+  auto as_bool = [](const std::string& v) { return v == "true" || v == "True" || v == "1" || v == "yes"; };
+  for (auto& e : kv) {
+    for (const Vec& v : vecs)
+      if (e.first == v.key) {
+        if ((int)e.second.size() != v.n) {
+          g_err = "viekf_config_load_yaml: key '" + e.first + "' has " + std::to_string(e.second.size()) + " values, expected " + std::to_string(v.n);
+          return VIEKF_ERR_ARG;
+        }
+        for (int i = 0; i < v.n; i++) v.dst[i] = atof(e.second[i].c_str());
+      }
+    if (e.second.size() == 1) {
+      if (e.first == "use_drag_term") c->use_drag_term = as_bool(e.second[0]);
+      if (e.first == "use_partial_update") c->use_partial_update = as_bool(e.second[0]);
+      if (e.first == "use_keyframe_reset") c->use_keyframe_reset = as_bool(e.second[0]);
+    }
+  }
+  return VIEKF_OK;
+}
+
 int viekf_batch_create(const viekf_config* cfg, int64_t B, int32_t N, int32_t device, viekf_batch** out) {
   if (!cfg || !out || B <= 0 || N < 0 || N > 64) return fail(VIEKF_ERR_ARG, "viekf_batch_create: bad argument (need B>0, 0<=N<=64)");
   int ndev = 0;
@@ -239,6 +356,11 @@ void viekf_batch_destroy(viekf_batch* h) {
   cudaFree(h->d_ids);
   cudaFree(h->d_res);
   cudaFree(h->d_x0);
+  cudaFree(h->d_stage);
+  cudaFree(h->d_res_stage);
+  cudaFree(h->d_tape_ev);
+  cudaFree(h->d_tape_ids);
+  cudaFree(h->d_tape_vals);
   if (h->stream) cudaStreamDestroy(h->stream);
   delete h;
 }
@@ -298,12 +420,11 @@ int viekf_batch_get_state(viekf_batch* h, int64_t first, int64_t count, double* 
   if (count == 0) return VIEKF_OK;
   CK(cudaSetDevice(h->device));
   const size_t bytes = sizeof(double) * (17 + 5 * h->N) * count;
-  double* d = nullptr;
-  CK(cudaMalloc(&d, bytes));
+  if (grow(&h->d_stage, &h->stage_cap, bytes) != cudaSuccess) return fail(VIEKF_ERR_NOMEM, "get_state: staging buffer");
+  double* d = (double*)h->d_stage;
   cudaError_t e = vk::launch_unpack_state(h->kp, first, count, d, h->stream);
   if (e == cudaSuccess) e = cudaMemcpyAsync(x, d, bytes, cudaMemcpyDeviceToHost, h->stream);
   if (e == cudaSuccess) e = cudaStreamSynchronize(h->stream);
-  cudaFree(d);
   if (e != cudaSuccess) return fail(VIEKF_ERR_CUDA, "get_state", e);
   return VIEKF_OK;
 }
@@ -315,8 +436,9 @@ int viekf_batch_get_covariance(viekf_batch* h, int64_t first, int64_t count, dou
   const int64_t n = 16 + 3 * h->N;
   // unpack in slabs so a large batch never needs a full dense copy on the device
   const int64_t slab = std::max<int64_t>(1, (int64_t)(256ll << 20) / (int64_t)(sizeof(double) * n * n));
-  double* d = nullptr;
-  CK(cudaMalloc(&d, sizeof(double) * n * n * std::min(slab, count)));
+  if (grow(&h->d_stage, &h->stage_cap, sizeof(double) * n * n * std::min(slab, count)) != cudaSuccess)
+    return fail(VIEKF_ERR_NOMEM, "get_covariance: staging buffer");
+  double* d = (double*)h->d_stage;
   cudaError_t e = cudaSuccess;
   for (int64_t o = 0; o < count && e == cudaSuccess; o += slab) {
     const int64_t c = std::min(slab, count - o);
@@ -324,10 +446,132 @@ int viekf_batch_get_covariance(viekf_batch* h, int64_t first, int64_t count, dou
     if (e == cudaSuccess) e = cudaMemcpyAsync(P + o * n * n, d, sizeof(double) * n * n * c, cudaMemcpyDeviceToHost, h->stream);
     if (e == cudaSuccess) e = cudaStreamSynchronize(h->stream);
   }
-  cudaFree(d);
   if (e != cudaSuccess) return fail(VIEKF_ERR_CUDA, "get_covariance", e);
   return VIEKF_OK;
 }
+
+int viekf_batch_get_covariance_diagonal(viekf_batch* h, int64_t first, int64_t count, double* dg) {
+  if (int rc = check_range(h, first, count, dg)) return rc;
+  if (count == 0) return VIEKF_OK;
+  CK(cudaSetDevice(h->device));
+  const size_t bytes = sizeof(double) * (16 + 3 * h->N) * count;
+  if (grow(&h->d_stage, &h->stage_cap, bytes) != cudaSuccess) return fail(VIEKF_ERR_NOMEM, "get_covariance_diagonal: staging buffer");
+  CK(vk::launch_unpack_diag(h->kp, first, count, (double*)h->d_stage, h->stream));
+  CK(cudaMemcpyAsync(dg, h->d_stage, bytes, cudaMemcpyDeviceToHost, h->stream));
+  CK(cudaStreamSynchronize(h->stream));
+  return VIEKF_OK;
+}
+
+// ---- feature read-back (vi_ekf.cpp:210-260): from the unpacked state and the id lists, on the host ----
+namespace {
+struct FeatView {
+  std::vector<double> x;
+  std::vector<int32_t> len, ids;
+  int mx = 0;
+};
+void host_zeta(const double* q, double* z) {  // q.rota(e_z): third column of R^T
+  const double w = q[0], x = q[1], y = q[2], zz = q[3];
+  z[0] = 2.0 * x * zz - 2.0 * w * y;
+  z[1] = 2.0 * y * zz + 2.0 * w * x;
+  z[2] = 1.0 - 2.0 * x * x - 2.0 * y * y;
+}
+}  // namespace
+static int feat_view(viekf_batch* h, int64_t first, int64_t count, FeatView& v) {
+  v.mx = 17 + 5 * h->N;
+  v.x.resize((size_t)v.mx * count);
+  v.len.resize((size_t)count);
+  v.ids.resize((size_t)std::max(h->N, 1) * count);
+  if (int rc = viekf_batch_get_state(h, first, count, v.x.data())) return rc;
+  return viekf_batch_get_features(h, first, count, v.len.data(), v.ids.data());
+}
+
+int viekf_batch_get_depths(viekf_batch* h, int64_t first, int64_t count, double* depths) {
+  if (int rc = check_range(h, first, count, depths)) return rc;
+  if (count == 0 || h->N == 0) return VIEKF_OK;
+  FeatView v;
+  if (int rc = feat_view(h, first, count, v)) return rc;
+  for (int64_t b = 0; b < count; b++)
+    for (int i = 0; i < h->N; i++) depths[b * h->N + i] = (i < v.len[b]) ? 1.0 / v.x[b * v.mx + 17 + 5 * i + 4] : NAN;
+  return VIEKF_OK;
+}
+
+int viekf_batch_get_qzetas(viekf_batch* h, int64_t first, int64_t count, double* qz) {
+  if (int rc = check_range(h, first, count, qz)) return rc;
+  if (count == 0 || h->N == 0) return VIEKF_OK;
+  FeatView v;
+  if (int rc = feat_view(h, first, count, v)) return rc;
+  for (int64_t b = 0; b < count; b++)
+    for (int i = 0; i < h->N; i++)
+      for (int k = 0; k < 4; k++) qz[(b * h->N + i) * 4 + k] = (i < v.len[b]) ? v.x[b * v.mx + 17 + 5 * i + k] : NAN;
+  return VIEKF_OK;
+}
+
+int viekf_batch_get_zetas(viekf_batch* h, int64_t first, int64_t count, double* zetas) {
+  if (int rc = check_range(h, first, count, zetas)) return rc;
+  if (count == 0 || h->N == 0) return VIEKF_OK;
+  FeatView v;
+  if (int rc = feat_view(h, first, count, v)) return rc;
+  for (int64_t b = 0; b < count; b++)
+    for (int i = 0; i < h->N; i++) {
+      double* z = zetas + (b * h->N + i) * 3;
+      if (i < v.len[b])
+        host_zeta(&v.x[b * v.mx + 17 + 5 * i], z);
+      else
+        z[0] = z[1] = z[2] = NAN;
+    }
+  return VIEKF_OK;
+}
+
+int viekf_batch_get_depth(viekf_batch* h, int32_t id, int64_t first, int64_t count, double* depth) {
+  if (int rc = check_range(h, first, count, depth)) return rc;
+  if (count == 0) return VIEKF_OK;
+  FeatView v;
+  if (int rc = feat_view(h, first, count, v)) return rc;
+  for (int64_t b = 0; b < count; b++) {
+    depth[b] = NAN;
+    for (int i = 0; i < v.len[b]; i++)
+      if (v.ids[b * h->N + i] == id) depth[b] = 1.0 / v.x[b * v.mx + 17 + 5 * i + 4];
+  }
+  return VIEKF_OK;
+}
+
+int viekf_batch_get_feat(viekf_batch* h, int32_t id, int64_t first, int64_t count, double* pixel) {
+  if (int rc = check_range(h, first, count, pixel)) return rc;
+  if (count == 0) return VIEKF_OK;
+  FeatView v;
+  if (int rc = feat_view(h, first, count, v)) return rc;
+  for (int64_t b = 0; b < count; b++) {
+    pixel[2 * b] = pixel[2 * b + 1] = NAN;
+    for (int i = 0; i < v.len[b]; i++)
+      if (v.ids[b * h->N + i] == id) {  // cam_F zeta / (e_z^T zeta) + cam_center (vi_ekf.cpp:254-259)
+        double z[3];
+        host_zeta(&v.x[b * v.mx + 17 + 5 * i], z);
+        pixel[2 * b] = h->cfg.focal_len[0] * z[0] / z[2] + h->cfg.cam_center[0];
+        pixel[2 * b + 1] = h->cfg.focal_len[1] * z[1] / z[2] + h->cfg.cam_center[1];
+      }
+  }
+  return VIEKF_OK;
+}
+
+int viekf_batch_set_imu_bias(viekf_batch* h, const double* b_g, const double* b_a) {
+  if (!h || !b_g || !b_a) return fail(VIEKF_ERR_ARG, "bad argument");
+  CK(cudaSetDevice(h->device));
+  if (grow(&h->d_stage, &h->stage_cap, 6 * sizeof(double)) != cudaSuccess) return fail(VIEKF_ERR_NOMEM, "set_imu_bias: staging buffer");
+  double v[6] = {b_g[0], b_g[1], b_g[2], b_a[0], b_a[1], b_a[2]};
+  CK(cudaMemcpyAsync(h->d_stage, v, sizeof(v), cudaMemcpyHostToDevice, h->stream));
+  CK(vk::launch_set_bias(h->kp, (const double*)h->d_stage, h->stream));
+  CK(cudaStreamSynchronize(h->stream));
+  return VIEKF_OK;
+}
+
+int viekf_batch_set_drag_term(viekf_batch* h, int32_t use_drag_term) {
+  if (!h) return fail(VIEKF_ERR_ARG, "null handle");
+  h->cfg.use_drag_term = use_drag_term ? 1 : 0;
+  h->kp.use_drag = h->cfg.use_drag_term;
+  return VIEKF_OK;
+}
+int viekf_batch_get_drag_term(const viekf_batch* h) { return h ? h->cfg.use_drag_term : 0; }
+
 
 static int fetch_meta(viekf_batch* h, int64_t first, int64_t count, std::vector<FilterMeta>& m) {
   m.resize((size_t)count);
@@ -895,20 +1139,51 @@ int viekf_batch_run_dev_tape(viekf_batch* h, const viekf_dev_tape* t, int64_t ev
 int viekf_batch_run_tape(viekf_batch* h, const viekf_tape* tape, uint8_t* results, int64_t result_first, int64_t result_count) {
   if (!h) return fail(VIEKF_ERR_ARG, "null handle");
   if (results && (result_first < 0 || result_count < 0 || result_first + result_count > h->B)) return fail(VIEKF_ERR_ARG, "bad result range");
-  viekf_dev_tape* d = nullptr;
-  if (int rc = viekf_batch_upload_tape(h, tape, &d)) return rc;
-  int rc = VIEKF_OK;
-  uint8_t* dres = nullptr;
-  cudaError_t e = cudaSuccess;
-  if (results && result_count > 0 && tape->n_events > 0) {
-    e = cudaMalloc(&dres, (size_t)result_count * tape->n_events);
-    if (e == cudaSuccess) e = cudaMemsetAsync(dres, 0xff, (size_t)result_count * tape->n_events, h->stream);
+  if (int rc = validate_tape(tape)) return rc;
+  if (tape->n_events == 0) return VIEKF_OK;
+  CK(cudaSetDevice(h->device));
+  // the tape goes to grow-only device buffers owned by the handle: one cudaMemcpyAsync per array, no allocation once warm
+  viekf_dev_tape d;
+  d.n_events = tape->n_events;
+  d.seed = tape->seed;
+  memcpy(d.bias_range, tape->imu_bias_range, sizeof(d.bias_range));
+  {
+    size_t cap = h->tape_ev_cap * sizeof(viekf_event);
+    if (grow((void**)&h->d_tape_ev, &cap, sizeof(viekf_event) * tape->n_events) != cudaSuccess) return fail(VIEKF_ERR_NOMEM, "run_tape: events");
+    h->tape_ev_cap = cap / sizeof(viekf_event);
+    d.ev = h->d_tape_ev;
+    CK(cudaMemcpyAsync(d.ev, tape->events, sizeof(viekf_event) * tape->n_events, cudaMemcpyHostToDevice, h->stream));
   }
-  if (e == cudaSuccess && tape->n_events > 0) rc = run_range(h, d, 0, tape->n_events, dres, result_first, dres ? result_count : 0);
-  if (rc == VIEKF_OK && e == cudaSuccess && dres) e = cudaMemcpyAsync(results, dres, (size_t)result_count * tape->n_events, cudaMemcpyDeviceToHost, h->stream);
+  if (tape->n_ids > 0 && tape->id_pool) {
+    size_t cap = h->tape_ids_cap * sizeof(int32_t);
+    if (grow((void**)&h->d_tape_ids, &cap, sizeof(int32_t) * tape->n_ids) != cudaSuccess) return fail(VIEKF_ERR_NOMEM, "run_tape: id pool");
+    h->tape_ids_cap = cap / sizeof(int32_t);
+    d.id_pool = h->d_tape_ids;
+    CK(cudaMemcpyAsync(d.id_pool, tape->id_pool, sizeof(int32_t) * tape->n_ids, cudaMemcpyHostToDevice, h->stream));
+  }
+  if (tape->values && tape->values_stride > 0) {
+    size_t cap = h->tape_vals_cap * sizeof(double);
+    const size_t need = sizeof(double) * tape->values_stride * h->B;
+    if (grow((void**)&h->d_tape_vals, &cap, need) != cudaSuccess) return fail(VIEKF_ERR_NOMEM, "run_tape: values");
+    h->tape_vals_cap = cap / sizeof(double);
+    d.values = h->d_tape_vals;
+    d.vstride = tape->values_stride;
+    CK(cudaMemcpyAsync(d.values, tape->values, need, cudaMemcpyHostToDevice, h->stream));
+  }
+  uint8_t* dres = nullptr;
+  const size_t res_bytes = (results && result_count > 0) ? (size_t)result_count * tape->n_events : 0;
+  if (res_bytes) {
+    if (grow(&h->d_res_stage, &h->res_cap, res_bytes) != cudaSuccess) return fail(VIEKF_ERR_NOMEM, "run_tape: results");
+    dres = (uint8_t*)h->d_res_stage;
+    CK(cudaMemsetAsync(dres, 0xff, res_bytes, h->stream));
+  }
+  int rc = run_range(h, &d, 0, tape->n_events, dres, result_first, dres ? result_count : 0);
+  cudaError_t e = cudaSuccess;
+  if (rc == VIEKF_OK && dres) e = cudaMemcpyAsync(results, dres, res_bytes, cudaMemcpyDeviceToHost, h->stream);
   if (e == cudaSuccess) e = cudaStreamSynchronize(h->stream);
-  cudaFree(dres);
-  viekf_batch_free_tape(h, d);
+  d.ev = nullptr;  // the buffers belong to the handle
+  d.id_pool = nullptr;
+  d.values = nullptr;
   if (rc != VIEKF_OK) return rc;
   if (e != cudaSuccess) return fail(VIEKF_ERR_CUDA, "run_tape", e);
   return VIEKF_OK;

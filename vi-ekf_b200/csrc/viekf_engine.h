@@ -81,6 +81,8 @@ cudaError_t launch_perturb(const KParams& p, uint64_t seed, cudaStream_t stream)
 // read-out: unpack to the reference's layouts
 cudaError_t launch_unpack_state(const KParams& p, int64_t first, int64_t count, double* x_out_dev, cudaStream_t stream);
 cudaError_t launch_unpack_cov(const KParams& p, int64_t first, int64_t count, double* P_out_dev, cudaStream_t stream);
+cudaError_t launch_unpack_diag(const KParams& p, int64_t first, int64_t count, double* d_out_dev, cudaStream_t stream);
+cudaError_t launch_set_bias(const KParams& p, const double* bg3_ba3_dev, cudaStream_t stream);
 // FP64 FMA probe
 cudaError_t fp64_probe(int device, double* tflops);
 

@@ -304,6 +304,37 @@ cudaError_t launch_unpack_cov(const KParams& p, int64_t first, int64_t count, do
   return cudaGetLastError();
 }
 
+// get_covariance_diagonal: [MAX_DX x count], dead entries 0
+__global__ void unpack_diag_kernel(const __grid_constant__ KParams p, int64_t first, int64_t count, double* out) {
+  const int n = 16 + 3 * p.N;
+  const int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= count * n) return;
+  const int64_t b = idx / n;
+  const int i = (int)(idx - b * n);
+  const int live = 16 + 3 * p.meta[first + b].len;
+  out[idx] = (i < live) ? p.P[(first + b) * p.ps + plo(i, i)] : 0.0;
+}
+cudaError_t launch_unpack_diag(const KParams& p, int64_t first, int64_t count, double* o, cudaStream_t stream) {
+  const int64_t tot = count * (16 + 3 * p.N);
+  unpack_diag_kernel<<<(unsigned)((tot + 255) / 256), 256, 0, stream>>>(p, first, count, o);
+  return cudaGetLastError();
+}
+
+// set_imu_bias(b_g, b_a): v = [b_g(3), b_a(3)]
+__global__ void set_bias_kernel(const __grid_constant__ KParams p, const double* v) {
+  const int64_t b = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (b >= p.B) return;
+  double* x = p.x + b * p.xs;
+  for (int k = 0; k < 3; k++) {
+    x[13 + k] = v[k];
+    x[10 + k] = v[3 + k];
+  }
+}
+cudaError_t launch_set_bias(const KParams& p, const double* v, cudaStream_t stream) {
+  set_bias_kernel<<<(unsigned)((p.B + 127) / 128), 128, 0, stream>>>(p, v);
+  return cudaGetLastError();
+}
+
 // ------------------------------------------------------------------------------------------------------------------
 // FP64 FMA throughput probe (roofline denominator of the compute-bound kernels)
 // ------------------------------------------------------------------------------------------------------------------
