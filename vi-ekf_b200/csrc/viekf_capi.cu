@@ -469,10 +469,10 @@ struct FeatView {
   std::vector<int32_t> len, ids;
   int mx = 0;
 };
-void host_zeta(const double* q, double* z) {  // q.rota(e_z): third column of R^T
+void host_zeta(const double* q, double* z) {  // q.rota(e_z) = R^T e_z: the third row of the passive R (quat.h:306-322)
   const double w = q[0], x = q[1], y = q[2], zz = q[3];
-  z[0] = 2.0 * x * zz - 2.0 * w * y;
-  z[1] = 2.0 * y * zz + 2.0 * w * x;
+  z[0] = 2.0 * x * zz + 2.0 * w * y;
+  z[1] = 2.0 * y * zz - 2.0 * w * x;
   z[2] = 1.0 - 2.0 * x * x - 2.0 * y * y;
 }
 }  // namespace
