@@ -172,6 +172,17 @@ int viekf_batch_perturb_x0(viekf_batch* h, uint64_t seed);
 /* get_state (vi_ekf.cpp:187-190): x is [MAX_X x count], instances first..first+count.  Only the live part
  * x[0 : 17+5*len) is defined; dead entries are written as 0. */
 int viekf_batch_get_state(viekf_batch* h, int64_t first, int64_t count, double* x);
+/* viekf_batch_get_state without any allocation.  NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).
+ * Same arguments and output as viekf_batch_get_state; the device scratch between the engine's layout and the copy to `x` is
+ * a fixed file-scope device array of VIEKF_NOALLOC_SCRATCH_DOUBLES doubles (2 MiB, held by every GPU that loads the library
+ * until the process exits) instead of the handle's grow-only staging buffer, so the call issues no cudaMalloc / cudaFree.
+ * count * MAX_X(N) must not exceed VIEKF_NOALLOC_SCRATCH_DOUBLES: VIEKF_ERR_ARG (with the limit in viekf_last_error)
+ * otherwise -- read the batch in several calls.  The array is shared by every handle and every call on a device and keeps the
+ * last call's contents; each call overwrites all of the part it copies out, so nothing needs clearing, but calls that overlap
+ * on the GPU (two handles' streams, two host threads) race on it: serialise them. */
+#define VIEKF_NOALLOC_SCRATCH_DOUBLES 262144
+int viekf_batch_get_state_noalloc(viekf_batch* h, int64_t first, int64_t count, double* x);
 /* get_covariance (vi_ekf.cpp:197-200): P is [MAX_DX x MAX_DX x count] column-major, reference ordering. */
 int viekf_batch_get_covariance(viekf_batch* h, int64_t first, int64_t count, double* P);
 /* get_len_features / tracked_features (include/vi_ekf.h:272,286): len[count], ids[N x count] (-1 padded). */

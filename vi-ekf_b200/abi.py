@@ -17,6 +17,7 @@ MEAS_SUCCESS, MEAS_GATED, MEAS_NAN, MEAS_INVALID, MEAS_NEW_FEATURE = range(5)
 MEAS_NONE = 255
 EV_PROP, EV_UPD, EV_INIT, EV_CLEAR, EV_KEEP, EV_STAT, EV_KFRESET = range(7)
 STAT_WIDTH = 40
+NOALLOC_SCRATCH_DOUBLES = 262144  # VIEKF_NOALLOC_SCRATCH_DOUBLES
 FLAG_NAN_STATE, FLAG_DEPTH_NAN_FIXED, FLAG_DEPTH_NEG_FIXED, FLAG_DEPTH_BIG_FIXED, FLAG_NAN_GAIN, FLAG_BACKWARD_DT = 1, 2, 4, 8, 16, 32
 
 
@@ -121,6 +122,7 @@ def load_library():
         "viekf_batch_set_x0": (i32, [vp, vp, i32]),
         "viekf_batch_perturb_x0": (i32, [vp, C.c_uint64]),
         "viekf_batch_get_state": (i32, [vp, i64, i64, vp]),
+        "viekf_batch_get_state_noalloc": (i32, [vp, i64, i64, vp]),
         "viekf_batch_get_covariance": (i32, [vp, i64, i64, vp]),
         "viekf_batch_get_features": (i32, [vp, i64, i64, vp, vp]),
         "viekf_batch_get_flags": (i32, [vp, i64, i64, vp, vp]),

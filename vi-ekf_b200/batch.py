@@ -62,6 +62,13 @@ class BatchVIEKF:
         self._chk(self.L.viekf_batch_get_state(self.h, first, count, _p(x)))
         return x
 
+    def get_state_noalloc(self, first=0, count=None):
+        """get_state through the fixed device scratch array: no cudaMalloc (operators' addition, include/viekf_batch.h)."""
+        count = self.B - first if count is None else count
+        x = np.zeros((count, self.MAX_X))
+        self._chk(self.L.viekf_batch_get_state_noalloc(self.h, first, count, _p(x)))
+        return x
+
     def get_covariance(self, first=0, count=None):
         count = self.B - first if count is None else count
         P = np.zeros((count, self.MAX_DX, self.MAX_DX))

@@ -10,6 +10,7 @@
 #include <algorithm>
 #include <array>
 #include <deque>
+#include <mutex>
 #include <string>
 #include <vector>
 #include "viekf_engine.h"
@@ -1226,6 +1227,54 @@ int viekf_batch_stats(viekf_batch* h, double* out, int32_t n_buckets) {
 }
 
 void* viekf_batch_stats_dev_ptr(viekf_batch* h) { return h ? (void*)h->kp.stats : nullptr; }
+
+// ---- read-back without any allocation (no counterpart in the reference) ------
+// The unpack kernel of get_state needs device scratch between the engine's layout and the copy to the caller's buffer.  Here
+// that scratch is a file-scope device array of fixed size instead of the handle's grow-only cudaMalloc staging, so the call can
+// be made where cudaMalloc is forbidden.  Every GPU that loads the library holds the 2 MiB until the process exits.
+static __device__ __align__(256) double g_noalloc_scratch[VIEKF_NOALLOC_SCRATCH_DOUBLES];
+// In host code `g_noalloc_scratch` is only a stand-in for the symbol, not a device address: the address is looked up once per
+// device, with that device current, and cached here.
+static const int NOALLOC_MAX_DEVICES = 64;
+static double* g_noalloc_ptr[NOALLOC_MAX_DEVICES] = {nullptr};
+static std::mutex g_noalloc_mutex;
+
+static int noalloc_scratch_for(int device, double** out) {
+  if (device < 0 || device >= NOALLOC_MAX_DEVICES) return fail(VIEKF_ERR_UNSUPPORTED, "get_state_noalloc: device ordinal beyond 63");
+  std::lock_guard<std::mutex> lock(g_noalloc_mutex);
+  if (!g_noalloc_ptr[device]) {
+    double* ptr = nullptr;
+    cudaError_t e = cudaGetSymbolAddress((void**)&ptr, g_noalloc_scratch);  // the caller has made `device` current
+    if (e != cudaSuccess || !ptr) return fail(VIEKF_ERR_CUDA, "get_state_noalloc: cudaGetSymbolAddress(g_noalloc_scratch)", e);
+    g_noalloc_ptr[device] = ptr;
+  }
+  *out = g_noalloc_ptr[device];
+  return VIEKF_OK;
+}
+
+int viekf_batch_get_state_noalloc(viekf_batch* h, int64_t first, int64_t count, double* x) {
+  if (int rc = check_range(h, first, count, x)) return rc;
+  if (count == 0) return VIEKF_OK;
+  const int64_t need = (int64_t)(17 + 5 * h->N) * count;
+  if (need > (int64_t)VIEKF_NOALLOC_SCRATCH_DOUBLES) {
+    char buf[256];
+    snprintf(buf, sizeof(buf),
+             "viekf_batch_get_state_noalloc: %lld instances x %d doubles = %lld doubles exceed the fixed scratch of %d doubles; "
+             "read fewer instances per call (at most %lld) or use viekf_batch_get_state",
+             (long long)count, 17 + 5 * h->N, (long long)need, (int)VIEKF_NOALLOC_SCRATCH_DOUBLES,
+             (long long)(VIEKF_NOALLOC_SCRATCH_DOUBLES / (17 + 5 * h->N)));
+    return fail(VIEKF_ERR_ARG, buf);
+  }
+  CK(cudaSetDevice(h->device));
+  double* d = nullptr;
+  if (int rc = noalloc_scratch_for(h->device, &d)) return rc;
+  // the kernel writes every one of the `need` entries (dead entries as 0), so nothing of the previous call's contents survives
+  // in the part that is copied out and nothing has to be cleared first
+  CK(vk::launch_unpack_state(h->kp, first, count, d, h->stream));
+  CK(cudaMemcpyAsync(x, d, sizeof(double) * need, cudaMemcpyDeviceToHost, h->stream));
+  CK(cudaStreamSynchronize(h->stream));
+  return VIEKF_OK;
+}
 
 int viekf_fp64_peak_probe(int32_t device, double* tflops) {
   if (!tflops) return fail(VIEKF_ERR_ARG, "null pointer");
