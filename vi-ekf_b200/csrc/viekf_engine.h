@@ -63,6 +63,10 @@ struct KParams {
 
 // threads cooperating on one filter, chosen from N; GROUP_TILE selects the register-tile executor (viekf_tile.cu)
 static const int GROUP_TILE = 1;
+// GROUP_OCTET selects the N = 0 executor with eight lanes per filter and the covariance in registers (viekf_octet.cu)
+static const int GROUP_OCTET = 8;
+size_t octet_smem_bytes();
+cudaError_t launch_octet(const KParams& p, int sm_count, cudaStream_t stream);
 int group_size_for(int N);
 // register-tile executor: tile warps for N (0 = N outside its range), shared memory per filter, launch
 int tile_warps_for(int N);

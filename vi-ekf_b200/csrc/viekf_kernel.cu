@@ -25,6 +25,7 @@ namespace vk {
 size_t smem_bytes_per_filter(int N) { return (size_t)make_layout(N).total * sizeof(double); }
 
 int group_size_for(int N) {
+  if (N == 0) return GROUP_OCTET;
   if (N <= 1) return 32;
   if (N <= 6) return 64;
   if (tile_warps_for(N) > 0) return GROUP_TILE;
@@ -203,6 +204,7 @@ static cudaError_t launch_g(const KParams& p, int sm_count, cudaStream_t stream)
 cudaError_t launch_tape(const KParams& p, int group, int sm_count, cudaStream_t stream) {
   switch (group) {
     case GROUP_TILE: return launch_tile(p, sm_count, stream);
+    case GROUP_OCTET: return launch_octet(p, sm_count, stream);
     case 32: return launch_g<32>(p, sm_count, stream);
     case 64: return launch_g<64>(p, sm_count, stream);
     case 128: return launch_g<128>(p, sm_count, stream);
