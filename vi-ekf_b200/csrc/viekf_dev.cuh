@@ -1342,9 +1342,9 @@ __device__ __forceinline__ int ev_update(Ctx<G>& c, const KParams& p, const viek
 // STAT
 // ------------------------------------------------------------------------------------------------------------------
 // e^T B^-1 e for the M x M block B of P picked by idx (M = 16: base error state, M = 6: position + attitude), by a
-// right-looking Cholesky spread over the lanes of one warp: lane i owns row i.  The subtractions hit every element in
+// right-looking Cholesky spread over the lanes of one warp (or of a W-lane segment of it, M <= W): lane i owns row i.  The subtractions hit every element in
 // the same k-ascending order as a scalar left-looking factorisation.  NaN when B is not positive definite.
-template <int M>
+template <int M, int W = 32>
 __device__ __forceinline__ double nees_warp(const double* P, const double* er, int lane) {
   auto idx = [](int i) { return (M == 16) ? i : (i < 3 ? i : i + 3); };
   const int li = lane < M ? lane : M - 1;
@@ -1356,16 +1356,16 @@ __device__ __forceinline__ double nees_warp(const double* P, const double* er, i
   bool bad = false;
 #pragma unroll
   for (int j = 0; j < M; j++) {
-    const double sjj = __shfl_sync(0xffffffffu, a[j], j);
+    const double sjj = __shfl_sync(0xffffffffu, a[j], j, W);
     bad |= !(sjj > 0.0);
     const double ljj = sqrt(sjj);
     const double lij = (lane == j) ? ljj : a[j] / ljj;
-    const double yj = __shfl_sync(0xffffffffu, r / ljj, j);
+    const double yj = __shfl_sync(0xffffffffu, r / ljj, j, W);
     q += yj * yj;
     if (lane > j) r -= lij * yj;
 #pragma unroll
     for (int k = j + 1; k < M; k++) {
-      const double lkj = __shfl_sync(0xffffffffu, lij, k);
+      const double lkj = __shfl_sync(0xffffffffu, lij, k, W);
       if (lane >= k) a[k] -= lij * lkj;
     }
   }

@@ -2,9 +2,9 @@
 //
 // Eight lanes own one filter, four filters share a warp: the 16 x 16 covariance lives in REGISTERS (lane s of the octet holds
 // the full rows s and s + 8, 32 doubles), the state and the small per-event matrices in shared memory (3.8 KB per filter, so
-// 48+ filters are resident per SM where the warp-per-filter mapping of viekf_kernel.cu holds 12).  Nothing wider than a warp
-// ever synchronises: all hand-offs are __syncwarp(), and the filters of a warp run the shared tape in lock-step by
-// construction.  Event semantics are those of viekf_kernel.cu (same reference citations):
+// 48 filters are resident per SM where the warp-per-filter mapping of viekf_kernel.cu holds 12).  Every hand-off inside an event
+// is a __syncwarp(); the filters of a warp run the shared tape in lock-step by construction, and the warps of a CTA meet at one
+// barrier per event so that they share the instruction stream.  Event semantics are those of viekf_kernel.cu (same reference citations):
 //   PROP    VIEKF::propagate_state + dynamics + boxplus                 (vi_ekf.cpp:262-318, vi_ekf_dyn.cpp:14-94)
 //   UPD     add_measurement bookkeeping + VIEKF::update + base h-models (vi_ekf_meas.cpp:130-147,196-352)
 //   INIT / CLEAR / KEEP  with NUM_FEATURES = 0: refuse / no-op / keyframe bookkeeping only (vi_ekf_feat.cpp:6-142)
@@ -20,10 +20,14 @@
 namespace vk {
 
 #ifndef VIEKF_OCTET_WPC
-#define VIEKF_OCTET_WPC 2  // warps per CTA (no CTA-wide barrier exists, this only sets the scheduling granularity)
+#define VIEKF_OCTET_WPC 4  // warps per CTA
+#endif
+#ifndef VIEKF_OCTET_LOCKSTEP
+#define VIEKF_OCTET_LOCKSTEP 1  // the warps of a CTA run the tape in event lock-step (one CTA barrier per event): they share the
+                                // instruction stream, 365 M -> 405 M filter-steps/s at 65,536 x 0 (stall_no_instruction was 3.4 of 12 cycles)
 #endif
 #ifndef VIEKF_OCTET_MINB
-#define VIEKF_OCTET_MINB 6  // CTAs per SM the register allocation must admit
+#define VIEKF_OCTET_MINB 3  // CTAs per SM the register allocation must admit
 #endif
 
 namespace oct {
@@ -38,7 +42,8 @@ enum {
   O_GD = 174,  // G_d rows 0..8 [54]
   O_X2 = 228,  // lower triangle of the new 9 x 9 block, stride 10 [90]
   O_XA = 318,  // exchange area [160]: continuous A rows (9 x 14) | U columns 0..8 (16 x 10) | P H^T, K (16 x 4 each) | packed P
-  O_TOTAL = 478
+  O_BIAS = 478,  // the instance's constant IMU bias (viekf_tape.imu_bias_range), drawn once per slice [6]
+  O_TOTAL = 484
 };
 enum { MS = 14, XS = 10 };
 
@@ -72,6 +77,25 @@ __device__ __forceinline__ void rows_to_packed(double* Pk, int sub, const double
 #pragma unroll
   for (int j = 0; j < 16; j++)
     if (j <= sub + 8) Pk[plo(sub + 8, j)] = Pb[j];
+}
+
+// Component k of the event's per-instance values (resolve_values of viekf_dev.cuh on the staged record, the instance's IMU bias
+// from the per-slice cache): shared z | per-instance value block, plus generated white noise and (PROP) the constant bias.
+__device__ __forceinline__ void oct_resolve(const KParams& p, const viekf_event& E, int64_t e, int64_t b, int64_t ginst, int k, double* s) {
+  const int kind = E.kind;
+  double v = (E.noise >= 0 && p.values) ? p.values[b * p.vstride + 8 * (int64_t)E.noise + k] : E.z[k];
+  if (p.seed) {
+    const double sg = E.sigma[k];
+    const double sgo = E.sigma[k ^ 1];
+    if (sg != 0.0 || sgo != 0.0) {
+      double nn[2];
+      const uint32_t key = (kind == VIEKF_EV_PROP && E.aux >= 0) ? (0x80000000u | (uint32_t)E.aux) : (uint32_t)e;
+      viekf_normal_pair(p.seed, (uint64_t)ginst, key, (uint32_t)(k >> 1), nn);
+      v += sg * nn[k & 1];
+    }
+    if (kind == VIEKF_EV_PROP && k < 6 && p.bias_range[k] != 0.0) v += s[O_BIAS + k];
+  }
+  s[O_ZV + k] = v;
 }
 
 // ------------------------------------------------------------------------------------------------------------------
@@ -187,7 +211,8 @@ __device__ __forceinline__ void oct_propagate(double* s, const KParams& p, const
   // ---- phase B: row r of M = A dt + A^2 dt^2 / 2 and of G_d = (I + A dt / 2 + A^2 dt^2 / 6) G dt (vi_ekf.cpp:302-303) ----
   {
     const double h2 = dt * dt / 2.0, h6 = dt * dt / 6.0, hd2 = dt / 2.0;
-    for (int r = sub; r < 9; r += 8) {
+    {
+      const int r = sub;
       double ar[13];
 #pragma unroll
       for (int k = 0; k < 13; k++) ar[k] = Ac[r * MS + k];
@@ -233,8 +258,43 @@ __device__ __forceinline__ void oct_propagate(double* s, const KParams& p, const
 #pragma unroll
       for (int q = 0; q < 6; q++) Gr[q] = gd[q];
     }
+    // row 8 (ATT z) is shared out by columns, two per lane; its part of I + A dt / 2 + A^2 dt^2 / 6 goes through a scratch row
+    if (sub < 7) {
+      const int c0 = 2 * sub;
+      double a0 = 0, a1 = 0;
+#pragma unroll
+      for (int k = 0; k < 6; k++) {
+        const double a8 = Ac[8 * MS + k];
+        const double2 av = *(const double2*)(Ac + (3 + k) * MS + c0);
+        a0 = fma(a8, av.x, a0);
+        a1 = fma(a8, av.y, a1);
+      }
+      const double2 a8c = *(const double2*)(Ac + 8 * MS + c0);
+      *(double2*)(s + O_M + 8 * MS + c0) = make_double2(a8c.x * dt + a0 * h2, a8c.y * dt + a1 * h2);
+      if (sub < 3) *(double2*)(s + O_X2 + c0) = make_double2(a8c.x * hd2 + a0 * h6, ((c0 == 4) ? 1.0 : 0.0) + a8c.y * hd2 + a1 * h6);
+    }
   }
   __syncwarp();
+  if (sub == 7) {  // G_d row 8 from the scratch row (read before the barrier that precedes the first write of X2)
+    const double* mf = s + O_X2;
+    const double sv[9] = {0, -vel.z, vel.y, vel.z, 0, -vel.x, -vel.y, vel.x, 0};
+    double* Gr = s + O_GD + 8 * 6;
+    if (p.use_drag) {
+      Gr[0] = 0.0;
+      Gr[1] = 0.0;
+      Gr[2] = -dt * mf[2];
+    } else {
+#pragma unroll
+      for (int q = 0; q < 3; q++) Gr[q] = -dt * mf[q];
+    }
+#pragma unroll
+    for (int cc = 0; cc < 3; cc++) {
+      double t = 0;
+#pragma unroll
+      for (int k = 0; k < 3; k++) t = fma(-mf[k], sv[k * 3 + cc], t);
+      Gr[3 + cc] = dt * (t - mf[3 + cc]);
+    }
+  }
   // ---- U = P (I + M)^T on the own rows, columns 0..8 ----
   double* X = s + O_XA;
   {
@@ -623,8 +683,7 @@ static __device__ __noinline__ void oct_stat_err(double* s, const KParams& p, co
       for (int i = 0; i < 6; i++) xt[10 + i] = v[i];
     }
     if (p.seed) {
-      double bi[6];
-      for (int k = 0; k < 6; k++) bi[k] = p.bias_range[k] * viekf_uniform_pm1(p.seed, (uint64_t)ginst, VIEKF_NOISE_EVENT_BIAS, k);
+      const double* bi = s + O_BIAS;
       Q4 qbu = ldq(p.qbu);
       V3 ba = rota(qbu, mk3(bi[0], bi[1], bi[2])), bg = rota(qbu, mk3(bi[3], bi[4], bi[5]));
       xt[10] += ba.x; xt[11] += ba.y; xt[12] += ba.z;
@@ -645,15 +704,44 @@ static __device__ __noinline__ void oct_stat_err(double* s, const KParams& p, co
     for (int i = 0; i < 7; i++) er[9 + i] = xt[10 + i] - x[10 + i];
   }
 }
-static __device__ __noinline__ void oct_stat_nees(double* sw, int lane) {
-  for (int f = 0; f < 4; f++) {
-    double* sf = sw + (size_t)f * O_TOTAL;
-    const double q16 = nees_warp<16>(sf + O_XA, sf + O_M, lane);
-    const double q6 = nees_warp<6>(sf + O_XA, sf + O_M, lane);
-    if (lane == 0) {
-      sf[O_M + 16] = q16;
-      sf[O_M + 17] = q6;
+// e^T B^-1 e for the 16 x 16 base block by the eight lanes of the filter: nees_warp<16> of viekf_dev.cuh (right-looking Cholesky,
+// same operation order per element) with the rows `sub` and `sub + 8` on each lane and 8-lane shuffles.
+static __device__ __forceinline__ double oct_nees16(const double* Pk, const double* er, int sub) {
+  double aa[8], ab[16];
+#pragma unroll
+  for (int j = 0; j < 8; j++) aa[j] = (j <= sub) ? Pk[plo(sub, j <= sub ? j : 0)] : 0.0;
+#pragma unroll
+  for (int j = 0; j < 16; j++) ab[j] = (j <= sub + 8) ? Pk[plo(sub + 8, j <= sub + 8 ? j : 0)] : 0.0;
+  double ra = er[sub], rb = er[sub + 8];
+  double q = 0;
+  bool bad = false;
+#pragma unroll
+  for (int j = 0; j < 16; j++) {
+    const double sjj = __shfl_sync(0xffffffffu, (j < 8) ? aa[j < 8 ? j : 0] : ab[j], j & 7, 8);
+    bad |= !(sjj > 0.0);
+    const double ljj = sqrt(sjj);
+    double la = 0.0, lb;
+    if (j < 8) la = (sub == j) ? ljj : aa[j < 8 ? j : 0] / ljj;
+    lb = (sub + 8 == j) ? ljj : ab[j] / ljj;
+    const double yj = __shfl_sync(0xffffffffu, ((j < 8) ? ra : rb) / ljj, j & 7, 8);
+    q += yj * yj;
+    if (j < 8 && sub > j) ra -= la * yj;
+    if (sub + 8 > j) rb -= lb * yj;
+#pragma unroll
+    for (int k = j + 1; k < 16; k++) {
+      const double lkj = __shfl_sync(0xffffffffu, (k < 8) ? la : lb, k & 7, 8);
+      if (k < 8 && sub >= k) aa[k < 8 ? k : 0] -= la * lkj;
+      if (sub + 8 >= k) ab[k] -= lb * lkj;
     }
+  }
+  return bad ? nan("") : q;
+}
+static __device__ __noinline__ void oct_stat_nees(double* s, int sub) {
+  const double q16 = oct_nees16(s + O_XA, s + O_M, sub);
+  const double q6 = nees_warp<6, 8>(s + O_XA, s + O_M, sub);
+  if (sub == 0) {
+    s[O_M + 16] = q16;
+    s[O_M + 17] = q6;
   }
 }
 // STAT (same sums as ev_stat of viekf_dev.cuh; the NEES factorisations run one filter at a time on the whole warp)
@@ -671,7 +759,7 @@ __device__ __forceinline__ void oct_stat(double* s, double* sw, const KParams& p
   rows_to_packed(Pk, sub, Pa, Pb);
   if (sub == 0) oct_stat_err(s, p, E, b, ginst);
   __syncwarp();
-  oct_stat_nees(sw, lane);
+  oct_stat_nees(s, sub);
   __syncwarp();
   if (healthy && valid) {
     const bool ok16 = isfinite(out[0]), ok6 = isfinite(out[1]);
@@ -701,10 +789,12 @@ __global__ void __launch_bounds__(32 * VIEKF_OCTET_WPC, VIEKF_OCTET_MINB) viekf_
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, sub = lane & 7, fo = lane >> 3;
   double* sw = smem + (size_t)(warp * 4) * O_TOTAL;
   double* s = sw + (size_t)fo * O_TOTAL;
-  const int64_t nwarps = (int64_t)gridDim.x * VIEKF_OCTET_WPC;
-  for (int64_t q0 = ((int64_t)blockIdx.x * VIEKF_OCTET_WPC + warp) * 4; q0 < p.B; q0 += nwarps * 4) {
-    int64_t b = q0 + fo;
-    const bool valid = b < p.B;  // a ragged last quad keeps its lanes (they take part in every __syncwarp) on a copy of the last filter
+  double* evb = smem + (size_t)(VIEKF_OCTET_WPC * 4) * O_TOTAL + warp * 64;  // two staged viekf_event records (31 doubles each) per warp
+  static_assert(sizeof(viekf_event) == 31 * sizeof(double), "event staging assumes 31 doubles per record");
+  // the trip count is uniform over the CTA (lock-step barrier); a warp or lane without a filter runs on a copy of the last one
+  for (int64_t q0 = (int64_t)blockIdx.x * (VIEKF_OCTET_WPC * 4); q0 < p.B; q0 += (int64_t)gridDim.x * (VIEKF_OCTET_WPC * 4)) {
+    int64_t b = q0 + warp * 4 + fo;
+    const bool valid = b < p.B;  // lanes without a filter still take part in every __syncwarp
     if (!valid) b = p.B - 1;
     const int64_t ginst = p.inst_off + b;
     FilterMeta& M = p.meta[b];
@@ -723,16 +813,25 @@ __global__ void __launch_bounds__(32 * VIEKF_OCTET_WPC, VIEKF_OCTET_MINB) viekf_
       s[O_X + sub] = gx[sub];
       s[O_X + sub + 8] = gx[sub + 8];
       if (sub == 0) s[O_X + 16] = gx[16];
-      if (sub < 6) s[O_UB + sub] = M.ub[sub];
+      if (sub < 6) {
+        s[O_UB + sub] = M.ub[sub];
+        s[O_BIAS + sub] = (p.seed && p.bias_range[sub] != 0.0) ? p.bias_range[sub] * viekf_uniform_pm1(p.seed, (uint64_t)ginst, VIEKF_NOISE_EVENT_BIAS, sub) : 0.0;
+      }
       rows_from_packed(p.P + b * p.ps, sub, Pa, Pb);
+      if (p.ev_count > 0 && lane < 31) evb[lane] = ((const double*)(p.ev + p.ev_first))[lane];
     }
     __syncwarp();
     // ---- run the tape slice ----
-    for (int64_t e = p.ev_first; e < p.ev_first + p.ev_count; e++) {
-      const viekf_event& E = p.ev[e];
+    for (int64_t rel = 0; rel < p.ev_count; rel++) {
+      const int64_t e = p.ev_first + rel;
+      const viekf_event& E = *(const viekf_event*)(evb + 32 * (int)(rel & 1));
+      // the next record travels through a register while this event runs and is parked in the other slot at the end
+      const bool more = rel + 1 < p.ev_count && lane < 31;
+      double nxt = 0.0;
+      if (more) nxt = ((const double*)(p.ev + e + 1))[lane];
       const int kind = E.kind;
       if (kind == VIEKF_EV_PROP || kind == VIEKF_EV_UPD) {
-        resolve_values(p, e, b, ginst, sub, s + O_ZV);
+        oct_resolve(p, E, e, b, ginst, sub, s);
         __syncwarp();
       }
       int result = VIEKF_MEAS_NONE;
@@ -758,7 +857,12 @@ __global__ void __launch_bounds__(32 * VIEKF_OCTET_WPC, VIEKF_OCTET_MINB) viekf_
         default:  // CLEAR: nothing is tracked
           break;
       }
+      if (more) evb[32 * (int)((rel + 1) & 1) + lane] = nxt;
+#if VIEKF_OCTET_LOCKSTEP
+      __syncthreads();
+#else
       __syncwarp();
+#endif
       if (p.results && sub == 0 && valid && b >= p.res_first && b < p.res_first + p.res_count)
         p.results[(b - p.res_first) * p.n_events + e] = (uint8_t)result;
     }
@@ -787,7 +891,7 @@ __global__ void __launch_bounds__(32 * VIEKF_OCTET_WPC, VIEKF_OCTET_MINB) viekf_
   }
 }
 
-size_t octet_smem_bytes() { return (size_t)O_TOTAL * 4 * VIEKF_OCTET_WPC * sizeof(double); }
+size_t octet_smem_bytes() { return ((size_t)O_TOTAL * 4 + 64) * VIEKF_OCTET_WPC * sizeof(double); }
 
 cudaError_t launch_octet(const KParams& p, int sm_count, cudaStream_t stream) {
   if (p.N != 0) return cudaErrorInvalidValue;
