@@ -123,3 +123,29 @@ def test_statistics_across_keyframe_reset(pkg, oracle_mod):
     rmse_pos = np.sqrt(st[:, 17:20] / np.maximum(st[:, 0:1], 1))
     rmse_yaw = np.sqrt(st[:, 25] / np.maximum(st[:, 0], 1))
     assert rmse_pos.max() < 0.05 and rmse_yaw.max() < 0.02, f"rmse_pos {rmse_pos.max()}, rmse_yaw {rmse_yaw.max()}"
+
+
+def test_reference_controller_stream_parity(pkg, oracle_mod):
+    """The same comparison on streams flown by the reference's own closed loop (refsim.py: NLC + PID + waypoint manager,
+    lib/multirotor_sim/src/controller.cpp:18-62,229-279), with the bench's noise model: engine == oracle."""
+    sim = pkg.sim
+    N, B, sample = 12, 48, 32
+    cfg = abi.default_config()
+    cfg.use_keyframe_reset = 0
+    truth = sim.simulate(cfg, N, n_imu=300, controller="reference")
+    ev, idp, info = sim.build_tape(truth, cfg, N, stat_every=20, depth_known=True)
+    nb = info["n_buckets"]
+    ref = _run_oracle(oracle_mod, sim, cfg, N, ev, idp, nb, sample)
+    bk = pkg.BatchVIEKF(cfg, B=B, N=N)
+    bk.stats_reset(nb)
+    bk.perturb_x0(sim.BENCH_SEED + 1)
+    res = bk.run_tape(ev, idp, results_first=0, results_count=sample, seed=sim.BENCH_SEED, bias_range=sim.BENCH_BIAS)
+    ok = ref["margins"][:, 0] > 1e-7
+    assert (~ok).sum() <= sample // 8
+    idx = [b for b in range(sample) if ok[b]]
+    assert np.array_equal(res[idx], ref["results"][idx])
+    x, P = bk.get_state(0, sample), bk.get_covariance(0, sample)
+    ln, ids = bk.get_features(0, sample)
+    for b in idx:
+        assert ln[b] == ref["len"][b] and list(ids[b][: ln[b]]) == list(ref["ids"][b][: ln[b]])
+        tapes.live_compare(x[b], P[b], ln[b], ref["x"][b], ref["P"][b], ref["len"][b], REL_TOL, f"reference-controller stream inst {b}")

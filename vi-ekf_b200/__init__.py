@@ -4,4 +4,4 @@ include/viekf_batch.h, CUDA in csrc/).  Import through __graft_entry__.load_pack
 from . import abi  # noqa: F401
 from .batch import BatchVIEKF  # noqa: F401
 from .tape import TapeBuilder  # noqa: F401
-from . import batch, logfmt, shard, sim, tape  # noqa: F401,E402
+from . import batch, logfmt, refsim, shard, sim, tape  # noqa: F401,E402

@@ -5,8 +5,11 @@ A reduced restatement of the parts of lib/multirotor_sim the reference's sim-dri
 (lib/multirotor_sim/src/dynamics.cpp:50-106), IMU synthesis (:59-64, src/simulator.cpp:384-403), ground-plane
 landmarks seen by a pinhole camera with features replaced as they leave the image (src/environment.cpp:46-78,
 src/simulator.cpp:406-488,680-701) and an altimeter (:492-502), flown over the waypoints of params/sim_params.yaml:19-28.
-The waypoint controller is a plain cascaded P controller (the reference's NLC/PID stack, controller.cpp / nlc.h, is not
-reproduced: only a smooth, dynamically consistent trajectory is needed).  Everything here is deterministic; the
+Two vehicles can fly the waypoints: `controller="reduced"` (default; a plain cascaded P controller on a first-order
+rate loop: a smooth, dynamically consistent trajectory, the one every committed fixture and bench number was produced with) and
+`controller="reference"`: the reference's own closed loop (nonlinear velocity controller, roll / pitch / yaw-rate PID, hover-throttle
+observer, waypoint manager, force / torque dynamics) as restated in refsim.py and pinned against the waypoint-arrival times the
+reference's test holds.  Everything here is deterministic; the
 per-instance sensor noise of a Monte-Carlo batch is drawn on the device (include/viekf_noise.h).
 
 The tape follows the order in which the reference's measurement queue ends up applying things:
@@ -77,7 +80,7 @@ class Truth:
 
 
 def simulate(cfg, N, n_imu=1000, imu_rate=200.0, cam_rate=30.0, alt_rate=25.0, dt=0.0005, drag=0.1, seed=1, speed=1.0,
-             img_size=(640.0, 480.0)):
+             img_size=(640.0, 480.0), controller="reduced"):
     """Flies the waypoints and records IMU samples (IMU frame, noise-free), camera frames with up to N tracked
     landmarks, and altimeter samples.  State: p (inertial NED), v (body), q (inertial->body), w (body)."""
     rng = np.random.default_rng(seed)
@@ -160,6 +163,17 @@ def simulate(cfg, N, n_imu=1000, imu_rate=200.0, cam_rate=30.0, alt_rate=25.0, d
 
     out = Truth()
     imu_every = int(round(1.0 / (imu_rate * dt)))
+    veh = con = None
+    ft = np.zeros(4)
+    if controller == "reference":
+        # the reference's vehicle and controller (refsim.py); the controller runs at the IMU rate as in Simulator::run
+        # (simulator.cpp:100-121: the time step is the IMU period), the dynamics on the finer grid with the forces held
+        from . import refsim
+        prm = dict(enable_dynamics_noise=False, drag_constant=drag)
+        veh = refsim.Vehicle(refsim.State(p, q, v, w), prm, seed)
+        con = refsim.ReferenceController(WAYPOINTS, prm)
+    elif controller != "reduced":
+        raise ValueError("controller must be 'reduced' or 'reference'")
     cam_every = int(np.ceil(1.0 / (cam_rate * dt) - 1e-9))   # ">= 1/rate" on the 0.5 ms grid (simulator.cpp:409): 67 steps at 30 Hz
     alt_every = int(round(1.0 / (alt_rate * dt))) if alt_rate > 0 else 0
     tracked = []  # [id, point]
@@ -168,9 +182,18 @@ def simulate(cfg, N, n_imu=1000, imu_rate=200.0, cam_rate=30.0, alt_rate=25.0, d
     n_steps = n_imu * imu_every
     while len(out.imu_t) < n_imu + 1:
         t = k * dt
-        T, w_cmd = control(p, v, q, w)
+        if veh is not None:
+            if k % imu_every == 0:
+                tc = t + imu_every * dt  # the reference's clock is advanced before the controller runs
+                con.get_commanded_state(tc)
+                ft = veh.low_level(con.compute_control(tc, veh.x), imu_every * dt)
+        else:
+            T, w_cmd = control(p, v, q, w)
         if k % imu_every == 0:
-            acc_b = np.array([0, 0, -T]) - drag * v  # specific force in the body frame (dynamics.cpp:62, p_b_u = 0)
+            if veh is not None:
+                acc_b = veh.imu(veh.x, ft)[0]
+            else:
+                acc_b = np.array([0, 0, -T]) - drag * v  # specific force in the body frame (dynamics.cpp:62, p_b_u = 0)
             out.imu_t.append(t)
             out.imu_u.append(np.concatenate([q_rotp(q_bu, acc_b), q_rotp(q_bu, w)]))
             out.x_true.append(x17(p, v, q))
@@ -203,7 +226,11 @@ def simulate(cfg, N, n_imu=1000, imu_rate=200.0, cam_rate=30.0, alt_rate=25.0, d
             out.frames.append((t, vis, x17(p, v, q)))
         if alt_every and k > 0 and k % alt_every == 0:
             out.alt.append((t, -p[2]))
-        p, v, q, w = step(p, v, q, w, T, w_cmd, dt)
+        if veh is not None:
+            veh.run(dt, ft)
+            p, v, q, w = veh.x.p, veh.x.v, veh.x.q, veh.x.w
+        else:
+            p, v, q, w = step(p, v, q, w, T, w_cmd, dt)
         k += 1
     out.imu_t = np.array(out.imu_t)
     out.imu_u = np.array(out.imu_u)
