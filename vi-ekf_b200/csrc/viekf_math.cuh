@@ -67,8 +67,31 @@ __device__ __forceinline__ Q4 otimes(Q4 a, Q4 b) {
             a.w * b.y - a.x * b.z + a.y * b.w + a.z * b.x, a.w * b.z + a.x * b.y - a.y * b.x + a.z * b.w};
 }
 __device__ __forceinline__ Q4 qinv(Q4 a) { return Q4{a.w, -a.x, -a.y, -a.z}; }
+// Quat::exp (quat.h:128-146): [cos(|v|/2), sin(|v|/2) v/|v|] for |v| > 1e-4, the normalised first-order form below it.
+// For 1e-4 < |v| < 0.25 -- every state correction and every propagate step of a healthy filter -- the two functions of |v|^2
+// are evaluated as truncated Maclaurin series in h^2 = |v|^2/4 (first neglected terms h^14/14! < 3e-24 and h^14/15!): no square
+// root, no division and no sincos argument reduction on what is the longest dependent chain of the state update (boxplus sits
+// on the x warp's critical path once per event).  The result is within an ulp of the sincos form.
 __device__ __forceinline__ Q4 qexp(V3 v) {
-  double n = norm(v);
+  const double n2 = dot(v, v);
+  if (n2 < 0.0625 && n2 > 1e-8) {
+    const double h2 = 0.25 * n2;
+    double cs = fma(h2, 1.0 / 479001600.0, -1.0 / 3628800.0);
+    double sc = fma(h2, 1.0 / 6227020800.0, -1.0 / 39916800.0);
+    cs = fma(cs, h2, 1.0 / 40320.0);
+    sc = fma(sc, h2, 1.0 / 362880.0);
+    cs = fma(cs, h2, -1.0 / 720.0);
+    sc = fma(sc, h2, -1.0 / 5040.0);
+    cs = fma(cs, h2, 1.0 / 24.0);
+    sc = fma(sc, h2, 1.0 / 120.0);
+    cs = fma(cs, h2, -0.5);
+    sc = fma(sc, h2, -1.0 / 6.0);
+    cs = fma(cs, h2, 1.0);
+    sc = fma(sc, h2, 1.0);
+    const double s = 0.5 * sc;  // sin(|v|/2) / |v|
+    return Q4{cs, s * v.x, s * v.y, s * v.z};
+  }
+  const double n = sqrt(n2);
   if (n > 1e-4) {
     double sn, cs;
     sincos(n / 2.0, &sn, &cs);  // one argument reduction for both
