@@ -141,27 +141,38 @@ __device__ __forceinline__ double qpitch(Q4 q) {
 }
 __device__ __forceinline__ double qyaw(Q4 q) { return atan2(2.0 * (q.w * q.z + q.x * q.y), 1.0 - 2.0 * (q.y * q.y + q.z * q.z)); }
 
+// q.rota(e_x), q.rota(e_y), q.rota(e_z) = the rows of the passive rotation matrix (Rmat above), written out: the generic rota()
+// spends two thirds of its multiplications on the zeros of the unit vector (x * 0 cannot be folded in IEEE arithmetic)
+__device__ __forceinline__ V3 rota_ex(Q4 q) {
+  return V3{1.0 - 2.0 * (q.y * q.y + q.z * q.z), 2.0 * (q.x * q.y + q.w * q.z), 2.0 * (q.x * q.z - q.w * q.y)};
+}
+__device__ __forceinline__ V3 rota_ey(Q4 q) {
+  return V3{2.0 * (q.x * q.y - q.w * q.z), 1.0 - 2.0 * (q.x * q.x + q.z * q.z), 2.0 * (q.y * q.z + q.w * q.x)};
+}
+__device__ __forceinline__ V3 rota_ez(Q4 q) {
+  return V3{2.0 * (q.x * q.z + q.w * q.y), 2.0 * (q.y * q.z - q.w * q.x), 1.0 - 2.0 * (q.x * q.x + q.y * q.y)};
+}
 // bearing-vector manifold: zeta = q.rota(e_z), T_zeta = [q.rota(e_x) q.rota(e_y)]
 __device__ __forceinline__ void zeta_T(Q4 q, V3& zeta, V3& T0, V3& T1) {
-  zeta = rota(q, mk3(0, 0, 1));
-  T0 = rota(q, mk3(1, 0, 0));
-  T1 = rota(q, mk3(0, 1, 0));
+  zeta = rota_ez(q);
+  T0 = rota_ex(q);
+  T1 = rota_ey(q);
 }
 // exp(T_zeta d) (x) q      (left multiplication)
 __device__ __forceinline__ Q4 qfeat_boxplus(Q4 q, double d0, double d1) {
-  V3 T0 = rota(q, mk3(1, 0, 0)), T1 = rota(q, mk3(0, 1, 0));
+  V3 T0 = rota_ex(q), T1 = rota_ey(q);
   V3 d = mk3(T0.x * d0 + T1.x * d1, T0.y * d0 + T1.y * d1, T0.z * d0 + T1.z * d1);
   return otimes(qexp(d), q);
 }
 // q_j [-] q_i
 __device__ __forceinline__ void qfeat_boxminus(Q4 qj, Q4 qi, double out[2]) {
-  V3 zi = rota(qi, mk3(0, 0, 1)), zj = rota(qj, mk3(0, 0, 1));
+  V3 zi = rota_ez(qi), zj = rota_ez(qj);
   if (norm(zi - zj) > 1e-8) {
     V3 s = cross(zi, zj);
     double ns = norm(s);
     s = mk3(s.x / ns, s.y / ns, s.z / ns);
     double th = acos(dot(zi, zj));
-    V3 T0 = rota(qi, mk3(1, 0, 0)), T1 = rota(qi, mk3(0, 1, 0));
+    V3 T0 = rota_ex(qi), T1 = rota_ey(qi);
     V3 ts = th * s;
     out[0] = dot(T0, ts);
     out[1] = dot(T1, ts);

@@ -314,22 +314,26 @@ __device__ __forceinline__ void init_tctx(TCtx<TW>& c, double* base) {
 // x <- x [+] d s (vi_ekf_helper.cpp:88-98) on the x warp: item i < len is feature i, item len is the base state; one item per lane,
 // all in one pass for len <= 31.  Both kinds of item share the expensive part -- q' = exp(v) (x) q or q (x) exp(v), with sincos,
 // a square root and a division inside exp -- so the base state does not cost a second pass through it.
-static __device__ __noinline__ void xw_boxplus(double* x, const double* d, double s, int len, int lane) {
+static __device__ __noinline__ void xw_boxplus(double* __restrict__ x, const double* __restrict__ d, double s, int len, int lane) {
+  // the 13 additive base components (POS, VEL | B_A, B_G, MU) one per lane: a single lane ran them as 13 dependent
+  // load / FMA / store round trips in front of the quaternion, on the critical path of every event
+  if (lane < 13) {
+    const int xi = lane < 6 ? lane : lane + 4, di = lane < 6 ? lane : lane + 3;
+    x[xi] = fma(d[di], s, x[xi]);
+  }
   for (int it = lane; it <= len; it += 32) {
     const bool isb = (it == len);
     double* xq = isb ? x + 6 : x + 17 + 5 * it;
     const Q4 q = ldq(xq);
     V3 dv;
     if (isb) {
-      for (int k = 0; k < 6; k++) x[k] += d[k] * s;
       dv = mk3(d[6] * s, d[7] * s, d[8] * s);
-      for (int k = 0; k < 7; k++) x[10 + k] += d[9 + k] * s;
     } else {
       const double* df = d + 16 + 3 * it;
       const double d0 = df[0] * s, d1 = df[1] * s;
-      const V3 T0 = rota(q, mk3(1, 0, 0)), T1 = rota(q, mk3(0, 1, 0));
+      const V3 T0 = rota_ex(q), T1 = rota_ey(q);
       dv = mk3(T0.x * d0 + T1.x * d1, T0.y * d0 + T1.y * d1, T0.z * d0 + T1.z * d1);
-      xq[4] += df[2] * s;
+      xq[4] = fma(df[2], s, xq[4]);
     }
     const Q4 e = qexp(dv);
     const Q4 a = isb ? q : e, b = isb ? e : q;  // base: q (x) exp(v); feature: exp(T_zeta d) (x) q
