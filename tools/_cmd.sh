@@ -1,9 +1,4 @@
 mkdir -p gpurun_out
-python -m pytest tests -m gpu -x -q > gpurun_out/r2_v14_pytest.log 2>&1; echo "pytest rc $?"; tail -3 gpurun_out/r2_v14_pytest.log
-python bench.py --no-cpu > gpurun_out/r2_v14_bench.json 2>gpurun_out/r2_v14_bench.err; python -c "
-import json
-d=json.loads(open('gpurun_out/r2_v14_bench.json').read().strip().splitlines()[-1])
-print(d['value'], d['e2e']['value'], d['per_launch_ms'])
-for k,v in d['secondary'].items(): print(k, v['value'])
-"
-VIEKF_LIB=$PWD/vi-ekf_b200/csrc/libviekf_b200_pht.so python tools/phase_timing.py 32768 > gpurun_out/r2_v14_phase_timing.txt 2>&1; cat gpurun_out/r2_v14_phase_timing.txt
+brief() { python -c "import json,sys; d=json.loads(open(sys.argv[1]).read().strip().splitlines()[-1]); print(sys.argv[2], '%.4g' % d['value'], d['per_launch_ms'])" $1 $2; }
+for g in 1 64 128; do VIEKF_GROUP=$g python bench.py --filters 65536 --features 8 --no-cpu --no-secondary > gpurun_out/n8_g$g.json 2>/dev/null; brief gpurun_out/n8_g$g.json N8_group$g; done
+for n in 1 2 4 6; do python bench.py --filters 65536 --features $n --no-cpu --no-secondary > gpurun_out/n$n.json 2>/dev/null; brief gpurun_out/n$n.json N$n; done

@@ -1010,10 +1010,22 @@ __device__ __forceinline__ int x_update(TCtx<TW>& c, const KParams& p, const vie
   bool bad = Mi[MI_HNAN] != 0;
   {
     const int npad = 16 + 3 * ((len + 1) & ~1);
-    for (int i = c.lane; i < npad; i += 32) {
-      const double2 h01 = v.Hv[i];
-      double ph[3] = {h01.x, h01.y, 0.0};
-      if (RD == 3) ph[2] = v.H2[i];
+    // the rows of all passes at once (loads first): three dependent shared-memory round trips in a row cost the x warp ~0.5 k cycles
+    constexpr int NIT = (16 + 3 * ((tile_cap<TW>() + 1) & ~1) + 31) / 32;
+    double2 h01[NIT];
+    double h2[NIT], lm[NIT];
+#pragma unroll
+    for (int u = 0; u < NIT; u++) {
+      const int i = c.lane + 32 * u;
+      const bool in = i < npad;
+      h01[u] = in ? v.Hv[i] : make_double2(0.0, 0.0);
+      h2[u] = (RD == 3 && in) ? v.H2[i] : 0.0;
+      lm[u] = (p.use_partial && in) ? c.lam[i] : 1.0;
+    }
+#pragma unroll
+    for (int u = 0; u < NIT; u++) {
+      const int i = c.lane + 32 * u;
+      const double ph[3] = {h01[u].x, h01[u].y, h2[u]};
       double k3[3] = {0, 0, 0};
 #pragma unroll
       for (int b = 0; b < RD; b++) {
@@ -1021,12 +1033,12 @@ __device__ __forceinline__ int x_update(TCtx<TW>& c, const KParams& p, const vie
 #pragma unroll
         for (int a = 0; a < RD; a++) s += ph[a] * Si[a][b];
         k3[b] = s;
-        bad |= (s != s);
+        bad |= (i < npad) && (s != s);
       }
       double d = 0;
 #pragma unroll
       for (int a = 0; a < RD; a++) d += k3[a] * res[a];
-      c.dx[i] = p.use_partial ? c.lam[i] * d : d;
+      if (i < npad) c.dx[i] = p.use_partial ? lm[u] * d : d;
     }
   }
   bad = __any_sync(0xffffffffu, bad);
