@@ -1,4 +1,10 @@
 mkdir -p gpurun_out
-brief() { python -c "import json,sys; d=json.loads(open(sys.argv[1]).read().strip().splitlines()[-1]); print(sys.argv[2], '%.4g' % d['value'], d['per_launch_ms'])" $1 $2; }
-for g in 1 64 128; do VIEKF_GROUP=$g python bench.py --filters 65536 --features 8 --no-cpu --no-secondary > gpurun_out/n8_g$g.json 2>/dev/null; brief gpurun_out/n8_g$g.json N8_group$g; done
-for n in 1 2 4 6; do python bench.py --filters 65536 --features $n --no-cpu --no-secondary > gpurun_out/n$n.json 2>/dev/null; brief gpurun_out/n$n.json N$n; done
+python -m torch.distributed.run --nnodes=1 --nproc-per-node 8 --master-addr 127.0.0.1 --master-port 29517 bench.py --gpus 8 --steps 5 --warmup 3 > gpurun_out/r2_v15_bench_8gpu.json 2> gpurun_out/r2_v15_bench_8gpu.err; echo "rc $?"
+python -c "
+import json
+d=json.loads(open('gpurun_out/r2_v15_bench_8gpu.json').read().strip().splitlines()[-1])
+print(d['value'], d['e2e']['value'], d['n_gpus'], d['per_launch_ms'])
+print(json.dumps(d.get('secondary'))[:1500])
+print(d.get('mc_stats'))
+"
+tail -5 gpurun_out/r2_v15_bench_8gpu.err
