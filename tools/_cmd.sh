@@ -1,10 +1,3 @@
 mkdir -p gpurun_out
-python -m torch.distributed.run --nnodes=1 --nproc-per-node 8 --master-addr 127.0.0.1 --master-port 29517 bench.py --gpus 8 --steps 5 --warmup 3 > gpurun_out/r2_v15_bench_8gpu.json 2> gpurun_out/r2_v15_bench_8gpu.err; echo "rc $?"
-python -c "
-import json
-d=json.loads(open('gpurun_out/r2_v15_bench_8gpu.json').read().strip().splitlines()[-1])
-print(d['value'], d['e2e']['value'], d['n_gpus'], d['per_launch_ms'])
-print(json.dumps(d.get('secondary'))[:1500])
-print(d.get('mc_stats'))
-"
-tail -5 gpurun_out/r2_v15_bench_8gpu.err
+VIEKF_GROUP=64 ncu --set full --clock-control none --import-source on -k regex:viekf_tape_kernel -s 3 -c 1 -f -o gpurun_out/r2_g64_n8 python bench.py --filters 65536 --features 8 --steps 1 --warmup 3 --no-cpu --no-secondary > gpurun_out/r2_g64_n8_ncu.log 2>&1; echo "rc $?"
+ncu --set full --clock-control none --import-source on -k regex:viekf_tape_kernel -s 3 -c 1 -f -o gpurun_out/r2_g32_n1 python bench.py --filters 65536 --features 1 --steps 1 --warmup 3 --no-cpu --no-secondary > gpurun_out/r2_g32_n1_ncu.log 2>&1; echo "rc $?"
