@@ -298,7 +298,6 @@ __device__ __forceinline__ void oct_propagate(double* s, const KParams& p, const
   // ---- U = P (I + M)^T on the own rows, columns 0..8 ----
   double* X = s + O_XA;
   {
-    double ua[9], ubb[9];
 #pragma unroll
     for (int c = 0; c < 9; c++) {
       double mc[14];
@@ -314,14 +313,9 @@ __device__ __forceinline__ void oct_propagate(double* s, const KParams& p, const
         a = fma(Pa[3 + k], mc[k], a);
         b = fma(Pb[3 + k], mc[k], b);
       }
-      ua[c] = a;
-      ubb[c] = b;
-    }
-#pragma unroll
-    for (int c = 0; c < 9; c++) {
-      X[sub * XS + c] = ua[c];
-      X[(sub + 8) * XS + c] = ubb[c];
-      if (adv) Pb[c] = ubb[c];  // rows >= 9 keep U (row 8 of lane 0 is replaced below)
+      // straight to the exchange area: the rows keep their old columns 3..8 (operands of the columns still to come)
+      X[sub * XS + c] = a;
+      X[(sub + 8) * XS + c] = b;
     }
   }
   __syncwarp();
@@ -377,8 +371,10 @@ __device__ __forceinline__ void oct_propagate(double* s, const KParams& p, const
     if (sub == 0) X2[8 * XS + 8] = v88 + p.Qx[8];
   }
   __syncwarp();
-  // ---- assemble the rows: mirrored 9 x 9 block, columns >= 9 of rows < 9 from U^T, process noise on the diagonal ----
+  // ---- assemble the rows: mirrored 9 x 9 block, columns >= 9 of rows < 9 from U^T, rows >= 9 keep U, process noise on the diagonal ----
   if (adv) {
+#pragma unroll
+    for (int c = 0; c < 9; c++) Pb[c] = X[(sub + 8) * XS + c];  // (row 8 of lane 0 is replaced below)
 #pragma unroll
     for (int j = 0; j < 9; j++) Pa[j] = X2[(j > sub ? j : sub) * XS + (j > sub ? sub : j)];
 #pragma unroll
