@@ -9,5 +9,5 @@ NVCC=/usr/local/cuda/bin/nvcc
 ARCH="-gencode arch=compute_100a,code=sm_100a"
 C=$ROOT/vi-ekf_b200/csrc
 $NVCC -O3 -std=c++17 -lineinfo $ARCH -Xcompiler -fPIC -Xptxas -v "$@" -c $C/viekf_octet.cu -o $ROOT/build_ab/oct_$TAG.o 2> $ROOT/build_ab/ptxas_oct_$TAG.log || { grep -i error $ROOT/build_ab/ptxas_oct_$TAG.log | head -20; exit 1; }
-$NVCC $ARCH -shared -o $ROOT/build_ab/lib_$TAG.so $ROOT/build_ab/oct_$TAG.o $C/viekf_kernel.o $C/viekf_tile.o $C/viekf_capi.o -lcudart
+$NVCC $ARCH -shared -o $ROOT/build_ab/lib_$TAG.so $ROOT/build_ab/oct_$TAG.o $C/viekf_kernel.o $C/viekf_tile.o $C/viekf_frag.o $C/viekf_capi.o -lcudart
 grep -A2 "octet_kernel" $ROOT/build_ab/ptxas_oct_$TAG.log | grep -v Compiling | tr '\n' ' '; echo

@@ -65,6 +65,10 @@ struct KParams {
 static const int GROUP_TILE = 1;
 // GROUP_OCTET selects the N = 0 executor with eight lanes per filter and the covariance in registers (viekf_octet.cu)
 static const int GROUP_OCTET = 8;
+// GROUP_FRAG selects the 1 <= N <= 8 executor with the covariance in FP64 tensor-core fragments, one warp per filter (viekf_frag.cu)
+static const int GROUP_FRAG = 2;
+int frag_filters_per_cta();
+cudaError_t launch_frag(const KParams& p, int sm_count, cudaStream_t stream);
 size_t octet_smem_bytes();
 cudaError_t launch_octet(const KParams& p, int sm_count, cudaStream_t stream);
 int group_size_for(int N);

@@ -1,0 +1,572 @@
+// viekf_frag.cu -- tape executor for 1 <= N <= 8 (BASELINE configs[2] at N = 8) with the covariance in FP64 TENSOR-CORE FRAGMENTS.
+//
+// One warp owns one filter.  The 40 x 40 covariance (n = 16 + 3 len <= 40, dead rows / columns exact zeros) lives in registers as
+// 5 x 5 blocks of mma.sync.m8n8k4.f64 accumulator fragments (lane (g, t) = (lane / 4, lane % 4) holds elements (g, 2t), (g, 2t + 1)
+// of every block: 100 registers), and the three O(n^2) / O(n^3) operations run on the FP64 tensor-core pipe:
+//   propagate   T = A P, P' = T A^T (+ G_d Qu G_d^T + Qx) block-wise, A = A_d read from the discretised rows in shared memory (17 of
+//               its 25 blocks are non-zero); an accumulator block used as an operand is converted by intra-quad shuffles: element
+//               (g, 4kk + t) lives in lane 4g + 2kk + t/2, register t % 2; a block of the symmetric P used as a B operand is the
+//               transposed read of its mirror block (vi_ekf.cpp:302-304)
+//   P H^T       every H has <= 6 non-zero columns: the owners of those columns scale their elements, a quad reduction sums them
+//   rank update Joseph form as P += (1 - a a^T) o (G K^T + K G^T), G = K S / 2 - P H^T: one DMMA per block (two for a 3-row
+//               residual) (vi_ekf_meas.cpp:254-265)
+// Everything else -- dynamics and discretisation, the ten measurement models, S^-1 / gate, boxplus, feature bookkeeping, keyframe
+// reset, statistics -- is the code of viekf_dev.cuh shared with the other executors, run by the same warp on the filter's shared-
+// memory block; events that touch the covariance element-wise (init / clear / keep / keyframe reset / STAT) spill the fragments to
+// the packed copy in shared memory, run the shared code and reload.  After every event the upper triangle is rebuilt from the lower
+// one (fragment transposes by shuffle), so the state at an event boundary is a function of the packed lower triangle only:
+// chunked = single launch and sharded = unsharded stay bit-identical.  Measured basis: tools/microbench/frag_n40_proto.cu (92 % of
+// the FP64 peak on the covariance algebra).
+#include "viekf_dev.cuh"
+
+namespace vk {
+
+#ifndef VIEKF_FRAG_WPC
+#define VIEKF_FRAG_WPC 4  // filters (= warps) per CTA, in event lock-step
+#endif
+#ifndef VIEKF_FRAG_MINB
+#define VIEKF_FRAG_MINB 2
+#endif
+
+namespace frg {
+constexpr int NB = 5;  // 8 x 8 blocks per side: n <= 40
+
+__device__ __forceinline__ void dmma(double& c0, double& c1, double a, double b) {
+  asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};" : "+d"(c0), "+d"(c1) : "d"(a), "d"(b));
+}
+// element (g, 4kk + t) of an accumulator block (c0, c1), for the lane (g, t): from lane 4g + 2kk + t/2, register t % 2
+__device__ __forceinline__ double frag_elem(double c0, double c1, int src, bool odd) {
+  const double x0 = __shfl_sync(0xffffffffu, c0, src), x1 = __shfl_sync(0xffffffffu, c1, src);
+  return odd ? x1 : x0;
+}
+// does block (I, K) of A_d = [[A_bb, 0], [A_fb, blkdiag(A_ff)]] hold a non-zero?  (features straddle the 8-row block boundaries)
+__host__ __device__ constexpr bool nzA(int I, int K) { return K < 2 || (I >= 2 && K >= 2 && (I - K <= 1 && K - I <= 1)); }
+
+// A_d(r, cc) from the discretised rows of prop_discretise (Abd: 16 x 16, Afd: feature rows of 16 base columns + the own 3 x 3 block)
+__device__ __forceinline__ double a_elem(const Ctx<32>& c, int r, int cc, int n) {
+  if (r >= n || cc >= n) return 0.0;
+  if (r < 16) return cc < 16 ? c.Abd[r * 16 + cc] : 0.0;
+  const int fr = r - 16;
+  if (cc < 16) return c.Afd[fr * 19 + cc];
+  const int i = fr / 3, k = cc - 16 - 3 * i;
+  return (k >= 0 && k < 3) ? c.Afd[fr * 19 + 16 + k] : 0.0;
+}
+
+// fragments <-> the packed lower triangle in shared memory (live prefix n only, as the load / store of the shared-memory executor)
+__device__ __forceinline__ void spill(const Ctx<32>& c, int n, const double (&c0)[NB][NB], const double (&c1)[NB][NB]) {
+  const int g = c.tid >> 2, t = c.tid & 3;
+#pragma unroll
+  for (int I = 0; I < NB; I++)
+#pragma unroll
+    for (int J = 0; J <= I; J++) {
+      const int r = 8 * I + g, cc = 8 * J + 2 * t;
+      if (r < n && cc <= r) c.P[plo(r, cc)] = c0[I][J];
+      if (r < n && cc + 1 <= r) c.P[plo(r, cc + 1)] = c1[I][J];
+    }
+  __syncwarp();
+}
+__device__ __forceinline__ void reload(const Ctx<32>& c, int n, double (&c0)[NB][NB], double (&c1)[NB][NB]) {
+  const int g = c.tid >> 2, t = c.tid & 3;
+  __syncwarp();
+#pragma unroll
+  for (int I = 0; I < NB; I++)
+#pragma unroll
+    for (int J = 0; J < NB; J++) {
+      const int r = 8 * I + g, cc = 8 * J + 2 * t;
+      c0[I][J] = (r < n && cc < n) ? c.P[psym(r, cc)] : 0.0;
+      c1[I][J] = (r < n && cc + 1 < n) ? c.P[psym(r, cc + 1)] : 0.0;
+    }
+}
+// upper triangle := transpose of the lower one: destination element (g, 2t + e) of block (J, I) is element (2t + e, g) of block
+// (I, J), in lane 4 (2t + e) + g / 2, register g % 2
+__device__ __forceinline__ void symmetrise(int lane, double (&c0)[NB][NB], double (&c1)[NB][NB]) {
+  const int g = lane >> 2, t = lane & 3;
+  const int sa = 8 * t + (g >> 1), sb = sa + 4;
+  const bool odd = g & 1;
+#pragma unroll
+  for (int I = 0; I < NB; I++)
+#pragma unroll
+    for (int J = 0; J <= I; J++) {
+      const double x00 = __shfl_sync(0xffffffffu, c0[I][J], sa), x01 = __shfl_sync(0xffffffffu, c1[I][J], sa);
+      const double x10 = __shfl_sync(0xffffffffu, c0[I][J], sb), x11 = __shfl_sync(0xffffffffu, c1[I][J], sb);
+      const double t0 = odd ? x01 : x00, t1 = odd ? x11 : x10;
+      if (I != J) {
+        c0[J][I] = t0;
+        c1[J][I] = t1;
+      } else {  // inside a diagonal block the elements above the diagonal take the value of their mirror
+        if (2 * t > g) c0[I][I] = t0;
+        if (2 * t + 1 > g) c1[I][I] = t1;
+      }
+    }
+}
+
+// fix_depth (vi_ekf_helper.cpp:128-156): every lane walks the features (uniform), the owner of a diagonal element applies the
+// covariance part; lane 0 keeps the flags / counters
+__device__ __forceinline__ void fix_depth(const Ctx<32>& c, const KParams& p, int len, double (&c0)[NB][NB], double (&c1)[NB][NB]) {
+  const int g = c.tid >> 2, t = c.tid & 3;
+  __syncwarp();
+  for (int i = 0; i < len; i++) {
+    double* rho = c.x + 17 + 5 * i + 4;
+    double r = *rho;
+    const double reset = p.depth_reset;
+    uint32_t fl = 0;
+    int nfix = 0, kind = 0;
+    double add = 0.0;
+    if (r != r) {
+      r = reset;
+      fl |= VIEKF_FLAG_DEPTH_NAN_FIXED;
+      nfix++;
+    }
+    if (r < 0.0) {
+      const double err = reset - r;
+      add = err * err;
+      kind = 1;
+      r = reset;
+      fl |= VIEKF_FLAG_DEPTH_NEG_FIXED;
+      nfix++;
+    } else if (r > 1e2) {
+      kind = 2;
+      r = reset;
+      fl |= VIEKF_FLAG_DEPTH_BIG_FIXED;
+      nfix++;
+    }
+    if (!nfix) continue;
+    __syncwarp();  // every lane has read rho
+    if (kind) {
+      const int d = 16 + 3 * i + 2, I = d >> 3, dg = d & 7;
+      if (g == dg && t == (dg >> 1)) {
+#pragma unroll
+        for (int II = 2; II < NB; II++)
+          if (II == I) {
+            double& e = (dg & 1) ? c1[II][II] : c0[II][II];
+            e = (kind == 1) ? e + add : p.P0f[2];
+          }
+      }
+    }
+    if (c.tid == 0) {
+      *rho = r;
+      c.sc[SC_FLAGS] |= (int)fl;
+      c.sc[SC_NFIX] += nfix;
+    }
+    __syncwarp();
+  }
+}
+
+}  // namespace frg
+using namespace frg;
+
+// ------------------------------------------------------------------------------------------------------------------
+// PROP: propagate_state (vi_ekf.cpp:262-318); dynamics, discretisation and boxplus are the shared code
+// ------------------------------------------------------------------------------------------------------------------
+__device__ __forceinline__ void frag_propagate(Ctx<32>& c, const KParams& p, const viekf_event& E, double (&c0)[NB][NB], double (&c1)[NB][NB]) {
+  double dt;
+  int len;
+  if (!prop_discretise(c, p, E, dt, len, 0)) return;
+  const int n = 16 + 3 * len;
+  const int lane = c.tid, g = lane >> 2, t = lane & 3;
+  const int src0 = (lane & ~3) + (t >> 1), src1 = src0 + 2;
+  const bool odd = t & 1;
+  // ---- T = A P ----
+  double t0[NB][NB], t1[NB][NB];
+#pragma unroll
+  for (int I = 0; I < NB; I++)
+#pragma unroll
+    for (int J = 0; J < NB; J++) t0[I][J] = t1[I][J] = 0.0;
+#pragma unroll
+  for (int K = 0; K < NB; K++)
+#pragma unroll
+    for (int kk = 0; kk < 2; kk++) {
+      double b[NB];
+#pragma unroll
+      for (int J = 0; J < NB; J++) b[J] = frag_elem(c0[J][K], c1[J][K], kk ? src1 : src0, odd);  // P(K,J)[4kk+t][g] = P(J,K)[g][4kk+t]
+#pragma unroll
+      for (int I = 0; I < NB; I++)
+        if (nzA(I, K)) {
+          const double a = a_elem(c, 8 * I + g, 8 * K + 4 * kk + t, n);
+#pragma unroll
+          for (int J = 0; J < NB; J++) dmma(t0[I][J], t1[I][J], a, b[J]);
+        }
+    }
+  // ---- P' = T A^T + (G_d Qu) G_d^T (overwrites P) ----
+#pragma unroll
+  for (int I = 0; I < NB; I++)
+#pragma unroll
+    for (int J = 0; J < NB; J++) c0[I][J] = c1[I][J] = 0.0;
+#pragma unroll
+  for (int K = 0; K < NB; K++)
+#pragma unroll
+    for (int kk = 0; kk < 2; kk++) {
+      double a[NB];
+#pragma unroll
+      for (int I = 0; I < NB; I++) a[I] = frag_elem(t0[I][K], t1[I][K], kk ? src1 : src0, odd);
+#pragma unroll
+      for (int J = 0; J < NB; J++)
+        if (nzA(J, K)) {
+          const double b = a_elem(c, 8 * J + g, 8 * K + 4 * kk + t, n);  // A(J,K)^T[4kk+t][g]
+#pragma unroll
+          for (int I = 0; I < NB; I++) dmma(c0[I][J], c1[I][J], a[I], b);
+        }
+    }
+#pragma unroll
+  for (int kk = 0; kk < 2; kk++) {
+    const int q = 4 * kk + t;
+    double a[NB], b[NB];
+#pragma unroll
+    for (int I = 0; I < NB; I++) {
+      const int r = 8 * I + g;
+      const double gd = (q < 6 && r < n) ? c.Gd[r * 6 + q] : 0.0;
+      b[I] = gd;
+      a[I] = (q < 6) ? gd * p.Qu[q < 6 ? q : 0] : 0.0;
+    }
+#pragma unroll
+    for (int I = 0; I < NB; I++)
+#pragma unroll
+      for (int J = 0; J < NB; J++) dmma(c0[I][J], c1[I][J], a[I], b[J]);
+  }
+  // process noise on the live diagonal (vi_ekf.cpp:304)
+#pragma unroll
+  for (int I = 0; I < NB; I++) {
+    const int r = 8 * I + g;
+    if (r < n && t == (g >> 1)) {
+      const double qx = (r < 16) ? p.Qx[r] : p.Qxf[(r - 16) % 3];
+      if (g & 1) c1[I][I] += qx; else c0[I][I] += qx;
+    }
+  }
+  // ---- state: x <- x [+] xdot dt, time, fix_depth ----
+  boxplus_inplace(c, c.dx, dt, len);
+  if (c.tid == 0) *c.tcur = E.t;
+  fix_depth(c, p, len, c0, c1);
+}
+
+// ------------------------------------------------------------------------------------------------------------------
+// UPD: the covariance-touching part of update() behind ev_update of viekf_dev.cuh (vi_ekf_meas.cpp:226-278)
+// ------------------------------------------------------------------------------------------------------------------
+struct FragCore {
+  Ctx<32>& c;
+  const KParams& p;
+  double (&c0)[NB][NB];
+  double (&c1)[NB][NB];
+
+  __device__ __forceinline__ bool init_feature(double l0, double l1, double depth) {
+    const int n = 16 + 3 * c.sc[SC_LEN];
+    spill(c, n, c0, c1);
+    const bool ok = do_init_feature(c, p, l0, l1, depth);
+    reload(c, 16 + 3 * c.sc[SC_LEN], c0, c1);
+    return ok;
+  }
+  __device__ __forceinline__ void fix_depth(int len) { frg::fix_depth(c, p, len, c0, c1); }
+
+  template <int RD>
+  __device__ __forceinline__ int run(const viekf_event& E, int n, int len, const HReg& H) {
+    constexpr int MC = 6;
+    const int lane = c.tid, g = lane >> 2, t = lane & 3;
+    int* cols = c.sc + SC_COUNT;
+    const int nmax = 16 + 3 * p.N;  // rows of the update workspace (the fragment grid covers 40)
+    UpdVec<32> v(c, nmax);
+    // ---- P H^T: the owners of the <= 6 non-zero columns scale their elements, the quad sums ----
+    double acc[NB][3];
+#pragma unroll
+    for (int I = 0; I < NB; I++) acc[I][0] = acc[I][1] = acc[I][2] = 0.0;
+#pragma unroll
+    for (int k = 0; k < MC; k++)
+      if (k < H.m) {
+        const int col = H.col[k], J = col >> 3, tt = (col & 7) >> 1;
+        const bool e = col & 1;
+        double pv[NB];
+#pragma unroll
+        for (int I = 0; I < NB; I++) {
+          double x0 = c0[I][0], x1 = c1[I][0];
+#pragma unroll
+          for (int JJ = 1; JJ < NB; JJ++)
+            if (JJ == J) {
+              x0 = c0[I][JJ];
+              x1 = c1[I][JJ];
+            }
+          pv[I] = (t == tt) ? (e ? x1 : x0) : 0.0;
+        }
+#pragma unroll
+        for (int I = 0; I < NB; I++)
+#pragma unroll
+          for (int a = 0; a < RD; a++) acc[I][a] = fma(pv[I], H.h[a * MC + k], acc[I][a]);
+      }
+#pragma unroll
+    for (int I = 0; I < NB; I++) {
+#pragma unroll
+      for (int a = 0; a < RD; a++) {
+        acc[I][a] += __shfl_xor_sync(0xffffffffu, acc[I][a], 1);
+        acc[I][a] += __shfl_xor_sync(0xffffffffu, acc[I][a], 2);
+      }
+      const int r = 8 * I + g;
+      if (t == 0 && r < n) {
+        v.Hv[r] = make_double2(acc[I][0], acc[I][1]);
+        if (RD == 3) v.H2[r] = acc[I][2];
+      }
+    }
+    if (lane == 0) cols[8] = H.hnan ? 1 : 0;
+    __syncwarp();
+    // ---- S = H P H^T + R, S^-1, Mahalanobis gate (the code of update_core) ----
+    double S[3][3], Si[3][3];
+    {
+      double ph[MC][3];
+#pragma unroll
+      for (int k = 0; k < MC; k++) {
+        const int ck = (k < H.m) ? H.col[k] : 0;
+        const double2 tt2 = v.Hv[ck];
+        ph[k][0] = tt2.x;
+        ph[k][1] = tt2.y;
+        ph[k][2] = (RD == 3) ? v.H2[ck] : 0.0;
+      }
+#pragma unroll
+      for (int a = 0; a < RD; a++)
+#pragma unroll
+        for (int b = 0; b < RD; b++) {
+          double s = 0;
+#pragma unroll
+          for (int k = 0; k < MC; k++)
+            if (k < H.m) s += H.h[a * MC + k] * ph[k][b];
+          S[a][b] = s + E.R[a + b * RD];
+        }
+    }
+    const double mahal = inverse_and_mahal<RD>(S, Si, H.res);
+    if (mahal > 9.0) {
+      if (lane == 0) c.sc[SC_NGATED] += 1;
+      return VIEKF_MEAS_GATED;  // early return: no fix_depth (vi_ekf_meas.cpp:238)
+    }
+    // ---- K = P H^T S^-1, G = K S / 2 - P H^T, lambda o (K r) ----
+    bool bad = false;
+    for (int i = lane; i < 8 * NB; i += 32) {
+      double k3[3] = {0, 0, 0}, g3[3] = {0, 0, 0};
+      double d = 0, av = 0;
+      if (i < n) {
+        const double2 h01 = v.Hv[i];
+        double ph[3] = {h01.x, h01.y, 0.0};
+        if (RD == 3) ph[2] = v.H2[i];
+#pragma unroll
+        for (int b = 0; b < RD; b++) {
+          double s = 0;
+#pragma unroll
+          for (int a = 0; a < RD; a++) s += ph[a] * Si[a][b];
+          k3[b] = s;
+          bad |= (s != s);
+        }
+#pragma unroll
+        for (int a = 0; a < RD; a++) d += k3[a] * H.res[a];
+#pragma unroll
+        for (int a = 0; a < RD; a++) {
+          double s = 0;
+#pragma unroll
+          for (int b = 0; b < RD; b++) s += k3[b] * S[b][a];
+          g3[a] = 0.5 * s - ph[a];
+        }
+        const double li = c.lam[i];
+        av = p.use_partial ? 1.0 - li : 0.0;
+        c.dx[i] = p.use_partial ? li * d : d;
+      }
+      // rows behind the live prefix are written as zeros: the fragment rows there are zero and stay zero
+      if (i < nmax) {
+        v.Kv[i] = make_double2(k3[0], k3[1]);
+        v.KSv[i] = make_double2(g3[0], g3[1]);
+        if (RD == 3) {
+          v.K2[i] = k3[2];
+          v.KS2[i] = g3[2];
+        }
+        v.av[i] = av;
+      }
+    }
+    if (__any_sync(0xffffffffu, bad)) cols[8] = 1;
+    __syncwarp();
+    if (!cols[8]) {
+      boxplus_inplace(c, c.dx, 1.0, len);
+      // ---- P += (1 - a a^T) o (G K^T + K G^T): A operand rows (g0 g1 k0 k1), B operand columns (k0 k1 g0 g1) ----
+      double a[NB], b[NB], a2[NB], b2[NB];
+#pragma unroll
+      for (int I = 0; I < NB; I++) {
+        const int r = 8 * I + g;
+        const bool in = r < nmax;
+        const double2 zero2 = make_double2(0.0, 0.0);
+        const double2 gI = in ? v.KSv[r] : zero2, kI = in ? v.Kv[r] : zero2;
+        a[I] = t == 0 ? gI.x : t == 1 ? gI.y : t == 2 ? kI.x : kI.y;
+        b[I] = t == 0 ? kI.x : t == 1 ? kI.y : t == 2 ? gI.x : gI.y;
+        if (RD == 3) {
+          const double g2 = in ? v.KS2[r] : 0.0, k2 = in ? v.K2[r] : 0.0;
+          a2[I] = t == 0 ? g2 : t == 2 ? k2 : 0.0;
+          b2[I] = t == 0 ? k2 : t == 2 ? g2 : 0.0;
+        }
+      }
+      if (p.use_partial) {
+#pragma unroll
+        for (int I = 0; I < NB; I++) {
+          const double ai = (8 * I + g < nmax) ? v.av[8 * I + g] : 0.0;
+#pragma unroll
+          for (int J = 0; J < NB; J++) {
+            double d0 = 0.0, d1 = 0.0;
+            dmma(d0, d1, a[I], b[J]);
+            if (RD == 3) dmma(d0, d1, a2[I], b2[J]);
+            const int cc = 8 * J + 2 * t;
+            const double aj0 = (cc < nmax) ? v.av[cc] : 0.0, aj1 = (cc + 1 < nmax) ? v.av[cc + 1] : 0.0;
+            c0[I][J] = fma(d0, fma(-ai, aj0, 1.0), c0[I][J]);
+            c1[I][J] = fma(d1, fma(-ai, aj1, 1.0), c1[I][J]);
+          }
+        }
+      } else {
+#pragma unroll
+        for (int I = 0; I < NB; I++)
+#pragma unroll
+          for (int J = 0; J < NB; J++) {
+            dmma(c0[I][J], c1[I][J], a[I], b[J]);
+            if (RD == 3) dmma(c0[I][J], c1[I][J], a2[I], b2[J]);
+          }
+      }
+    } else if (lane == 0) {
+      c.sc[SC_FLAGS] |= VIEKF_FLAG_NAN_GAIN;
+      c.sc[SC_NNAN] += 1;
+    }
+    frg::fix_depth(c, p, len, c0, c1);
+    return VIEKF_MEAS_SUCCESS;
+  }
+};
+
+// ------------------------------------------------------------------------------------------------------------------
+// the persistent tape executor (skeleton of viekf_tape_kernel<32>: same shared-memory block per filter, same load / store)
+// ------------------------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(32 * VIEKF_FRAG_WPC, VIEKF_FRAG_MINB) viekf_frag_kernel(const __grid_constant__ KParams p) {
+  extern __shared__ __align__(16) double smem[];
+  constexpr int G = 32, GPC = VIEKF_FRAG_WPC;
+  const Layout L = make_layout(p.N);
+  Ctx<32> c;
+  c.gi = threadIdx.x / G;
+  c.tid = threadIdx.x % G;
+  double* base = smem + (size_t)c.gi * L.total;
+  c.x = base + L.x; c.P = base + L.P; c.lam = base + L.lam; c.dx = base + L.dx; c.Abd = base + L.Abd; c.AbT = base + L.AbT; c.T = base + L.T;
+  c.Ac = base + L.Ac; c.Gb = base + L.Gb; c.Afd = base + L.Afd; c.Gd = base + L.Gd; c.Y = base + L.Y; c.upd = base + L.upd;
+  c.sm = base + L.small;
+  c.ids = (int*)(base + L.ids);
+  c.rm = c.ids + p.N;
+  c.sc = c.rm + p.N;
+  c.tcur = c.sm + SM_T;
+  const int nmax = 16 + 3 * p.N;
+  for (int i = c.tid; i < nmax; i += G) c.lam[i] = (i < 16) ? p.lam[i] : p.lamf[(i - 16) % 3];
+  for (int64_t b0 = (int64_t)blockIdx.x * GPC; b0 < p.B; b0 += (int64_t)gridDim.x * GPC) {
+    const int64_t b = b0 + c.gi;
+    if (b >= p.B) {  // ragged last round: keep the barrier count of the warps that do have a filter
+      for (int64_t e = 0; e < p.ev_count; e++) __syncthreads();
+      continue;
+    }
+    c.b = b;
+    const int64_t ginst = p.inst_off + b;
+    FilterMeta& M = p.meta[b];
+    // ---- load the filter: meta, ids, live part of x and of the packed P; P then moves into the fragments ----
+    __syncwarp();
+    const int len0 = M.len;
+    if (c.tid == 0) {
+      c.sc[SC_LEN] = len0; c.sc[SC_NEXT] = M.next_id; c.sc[SC_STARTED] = M.started; c.sc[SC_FLAGS] = (int)M.flags;
+      c.sc[SC_NGATED] = (int)M.n_gated; c.sc[SC_NFIX] = (int)M.n_fix; c.sc[SC_NNAN] = (int)M.n_nan_gain; c.sc[SC_NKF] = M.n_kf;
+      *c.tcur = M.t;
+      for (int k = 0; k < 6; k++) c.sm[SM_UB + k] = M.ub[k];
+    }
+    for (int i = c.tid; i < len0; i += G) c.ids[i] = p.ids[b * p.N + i];
+    {
+      const double* gx = p.x + b * p.xs;
+      const int nx = 17 + 5 * len0;
+      for (int i = c.tid; i < nx; i += G) c.x[i] = gx[i];
+      const double2* gP = (const double2*)(p.P + b * p.ps);
+      double2* sP = (double2*)c.P;
+      const int n0 = 16 + 3 * len0;
+      const int np2 = (n0 * (n0 + 1) / 2 + 1) >> 1;
+      for (int i = c.tid; i < np2; i += G) sP[i] = gP[i];
+    }
+    if (p.ev_count > 0 && c.tid < 8) resolve_values(p, p.ev_first, b, ginst, c.tid, c.sm + SM_ZV);
+    double c0[NB][NB], c1[NB][NB];
+    reload(c, 16 + 3 * len0, c0, c1);
+    __syncwarp();
+    // ---- run the tape slice ----
+    for (int64_t e = p.ev_first; e < p.ev_first + p.ev_count; e++) {
+      const viekf_event& E = p.ev[e];
+      const int kind = E.kind;
+      c.zv = c.sm + SM_ZV + 8 * (int)((e - p.ev_first) & 1);
+      if (e + 1 < p.ev_first + p.ev_count && c.tid < 8)
+        resolve_values(p, e + 1, b, ginst, c.tid, c.sm + SM_ZV + 8 * (int)((e + 1 - p.ev_first) & 1));
+      int result = VIEKF_MEAS_NONE;
+      if (kind == VIEKF_EV_PROP) {
+        frag_propagate(c, p, E, c0, c1);
+        symmetrise(c.tid, c0, c1);
+      } else if (kind == VIEKF_EV_UPD) {
+        FragCore core{c, p, c0, c1};
+        result = ev_update(c, p, E, core);
+        symmetrise(c.tid, c0, c1);
+      } else {
+        // events that touch the covariance element by element run the shared code on the packed copy
+        spill(c, 16 + 3 * c.sc[SC_LEN], c0, c1);
+        switch (kind) {
+          case VIEKF_EV_INIT:
+            result = do_init_feature(c, p, c.zv[0], c.zv[1], E.z[4]) ? 1 : 0;
+            break;
+          case VIEKF_EV_CLEAR:
+            do_clear_feature(c, p, find_feature(c, E.id));
+            break;
+          case VIEKF_EV_KEEP:
+            do_keep_only(c, p, p.id_pool + E.ids_off, E.n_ids);
+            break;
+          case VIEKF_EV_KFRESET:
+            do_keyframe_reset(c, p);
+            break;
+          case VIEKF_EV_STAT:
+            ev_stat(c, p, E, ginst, [&]() { return smem_nan_scan(c); });
+            break;
+          default:
+            break;
+        }
+        reload(c, 16 + 3 * c.sc[SC_LEN], c0, c1);
+      }
+      __syncthreads();
+      if (p.results && c.tid == 0 && b >= p.res_first && b < p.res_first + p.res_count)
+        p.results[(b - p.res_first) * p.n_events + e] = (uint8_t)result;
+    }
+    // ---- store the filter ----
+    spill(c, 16 + 3 * c.sc[SC_LEN], c0, c1);
+    latch_nan_state(c, smem_nan_scan(c));  // NaNsInTheHouse at the end of the slice
+    const int len1 = c.sc[SC_LEN];
+    if (c.tid == 0) {
+      M.len = len1; M.next_id = c.sc[SC_NEXT]; M.started = c.sc[SC_STARTED]; M.flags = (uint32_t)c.sc[SC_FLAGS];
+      M.n_gated = (uint32_t)c.sc[SC_NGATED]; M.n_fix = (uint32_t)c.sc[SC_NFIX]; M.n_nan_gain = (uint32_t)c.sc[SC_NNAN]; M.n_kf = c.sc[SC_NKF];
+      M.t = *c.tcur;
+      for (int k = 0; k < 6; k++) M.ub[k] = c.sm[SM_UB + k];
+    }
+    for (int i = c.tid; i < len1; i += G) p.ids[b * p.N + i] = c.ids[i];
+    {
+      double* gx = p.x + b * p.xs;
+      const int nx = 17 + 5 * len1;
+      for (int i = c.tid; i < nx; i += G) gx[i] = c.x[i];
+      double2* gP = (double2*)(p.P + b * p.ps);
+      const double2* sP = (const double2*)c.P;
+      const int n1 = 16 + 3 * len1;
+      const int np2 = (n1 * (n1 + 1) / 2 + 1) >> 1;
+      for (int i = c.tid; i < np2; i += G) gP[i] = sP[i];
+    }
+    __syncwarp();
+  }
+}
+
+int frag_filters_per_cta() { return VIEKF_FRAG_WPC; }
+
+cudaError_t launch_frag(const KParams& p, int sm_count, cudaStream_t stream) {
+  if (p.N < 1 || p.N > 8) return cudaErrorInvalidValue;
+  constexpr int GPC = VIEKF_FRAG_WPC;
+  const size_t smem = smem_bytes_per_filter(p.N) * GPC;
+  cudaError_t e = cudaFuncSetAttribute(viekf_frag_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  if (e != cudaSuccess) return e;
+  e = cudaFuncSetAttribute(viekf_frag_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, (int)cudaSharedmemCarveoutMaxShared);
+  if (e != cudaSuccess) return e;
+  int occ = 0;
+  e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, viekf_frag_kernel, 32 * GPC, smem);
+  if (e != cudaSuccess) return e;
+  if (occ < 1) return cudaErrorInvalidConfiguration;
+  const int64_t need = (p.B + GPC - 1) / GPC;
+  int64_t grid = (int64_t)sm_count * occ;  // persistent: a whole number of waves of the SM count
+  if (need < grid) grid = need;
+  if (grid < 1) grid = 1;
+  viekf_frag_kernel<<<(unsigned)grid, 32 * GPC, smem, stream>>>(p);
+  return cudaGetLastError();
+}
+
+}  // namespace vk

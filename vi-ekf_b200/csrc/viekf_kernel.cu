@@ -205,6 +205,7 @@ cudaError_t launch_tape(const KParams& p, int group, int sm_count, cudaStream_t 
   switch (group) {
     case GROUP_TILE: return launch_tile(p, sm_count, stream);
     case GROUP_OCTET: return launch_octet(p, sm_count, stream);
+    case GROUP_FRAG: return launch_frag(p, sm_count, stream);
     case 32: return launch_g<32>(p, sm_count, stream);
     case 64: return launch_g<64>(p, sm_count, stream);
     case 128: return launch_g<128>(p, sm_count, stream);
