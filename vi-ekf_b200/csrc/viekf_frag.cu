@@ -105,7 +105,16 @@ __device__ __forceinline__ void symmetrise(int lane, double (&c0)[NB][NB], doubl
 __device__ __forceinline__ void fix_depth(const Ctx<32>& c, const KParams& p, int len, double (&c0)[NB][NB], double (&c1)[NB][NB]) {
   const int g = c.tid >> 2, t = c.tid & 3;
   __syncwarp();
-  for (int i = 0; i < len; i++) {
+  // lane i looks at feature i; nothing to fix is the common case and costs one ballot
+  bool need = false;
+  if (c.tid < len) {
+    const double r = c.x[17 + 5 * c.tid + 4];
+    need = (r != r) || (r < 0.0) || (r > 1e2);
+  }
+  unsigned todo = __ballot_sync(0xffffffffu, need);
+  while (todo) {
+    const int i = __ffs(todo) - 1;
+    todo &= todo - 1;
     double* rho = c.x + 17 + 5 * i + 4;
     double r = *rho;
     const double reset = p.depth_reset;
@@ -130,7 +139,6 @@ __device__ __forceinline__ void fix_depth(const Ctx<32>& c, const KParams& p, in
       fl |= VIEKF_FLAG_DEPTH_BIG_FIXED;
       nfix++;
     }
-    if (!nfix) continue;
     __syncwarp();  // every lane has read rho
     if (kind) {
       const int d = 16 + 3 * i + 2, I = d >> 3, dg = d & 7;
@@ -155,6 +163,27 @@ __device__ __forceinline__ void fix_depth(const Ctx<32>& c, const KParams& p, in
 }  // namespace frg
 using namespace frg;
 
+// resolve_values of viekf_dev.cuh with the instance's constant IMU bias taken from a per-slice cache (sm[SM_BIAS .. +5])
+enum { SM_BIAS = 62 };
+__device__ __forceinline__ void frag_resolve(const KParams& p, int64_t e, int64_t b, int64_t ginst, int k, const double* bias, double* out) {
+  const viekf_event& E = p.ev[e];
+  const int kind = E.kind;
+  if (!(kind == VIEKF_EV_PROP || kind == VIEKF_EV_UPD || kind == VIEKF_EV_INIT)) return;
+  double v = (E.noise >= 0 && p.values) ? p.values[b * p.vstride + 8 * (int64_t)E.noise + k] : E.z[k];
+  if (p.seed) {
+    const double sg = E.sigma[k];
+    const double sgo = E.sigma[k ^ 1];
+    if (sg != 0.0 || sgo != 0.0) {
+      double nn[2];
+      const uint32_t key = (kind == VIEKF_EV_PROP && E.aux >= 0) ? (0x80000000u | (uint32_t)E.aux) : (uint32_t)e;
+      viekf_normal_pair(p.seed, (uint64_t)ginst, key, (uint32_t)(k >> 1), nn);
+      v += sg * nn[k & 1];
+    }
+    if (kind == VIEKF_EV_PROP && k < 6 && p.bias_range[k] != 0.0) v += bias[k];
+  }
+  out[k] = v;
+}
+
 // ------------------------------------------------------------------------------------------------------------------
 // PROP: propagate_state (vi_ekf.cpp:262-318); dynamics, discretisation and boxplus are the shared code
 // ------------------------------------------------------------------------------------------------------------------
@@ -166,6 +195,29 @@ __device__ __forceinline__ void frag_propagate(Ctx<32>& c, const KParams& p, con
   const int lane = c.tid, g = lane >> 2, t = lane & 3;
   const int src0 = (lane & ~3) + (t >> 1), src1 = src0 + 2;
   const bool odd = t & 1;
+  // dense copy of blkdiag(A_ff) (3N x 3N, row stride 3N) so that every operand element of A is one load off a per-lane row base:
+  // in the packed-P area (stale while the fragments hold P) at N = 8, in the AbT | T arrays (unused by this executor) below
+  const int S = 3 * p.N;
+  double* Aff = (9 * p.N * p.N <= 512) ? c.AbT : c.P;
+  for (int i = lane; i < S * S; i += 32) Aff[i] = 0.0;
+  __syncwarp();
+  if (lane < len) {
+#pragma unroll
+    for (int a = 0; a < 3; a++)
+#pragma unroll
+      for (int k = 0; k < 3; k++) Aff[(3 * lane + a) * S + 3 * lane + k] = c.Afd[(3 * lane + a) * 19 + 16 + k];
+  }
+  __syncwarp();
+  // A(8I + g, 8K + 4kk + t): rows < 16 from Abd, feature rows from Afd (base columns) / Aff (feature columns); dead rows are zero
+  auto a_op = [&](int I, int K, int kk) -> double {
+    const int col = 8 * K + 4 * kk + t;
+    if (I < 2) return c.Abd[(8 * I + g) * 16 + col];  // K < 2 here
+    const int fr = 8 * (I - 2) + g;
+    if (fr >= 3 * len) return 0.0;
+    if (K < 2) return c.Afd[fr * 19 + col];
+    const int fc = col - 16;
+    return fc < S ? Aff[fr * S + fc] : 0.0;
+  };
   // ---- T = A P ----
   double t0[NB][NB], t1[NB][NB];
 #pragma unroll
@@ -182,7 +234,7 @@ __device__ __forceinline__ void frag_propagate(Ctx<32>& c, const KParams& p, con
 #pragma unroll
       for (int I = 0; I < NB; I++)
         if (nzA(I, K)) {
-          const double a = a_elem(c, 8 * I + g, 8 * K + 4 * kk + t, n);
+          const double a = a_op(I, K, kk);
 #pragma unroll
           for (int J = 0; J < NB; J++) dmma(t0[I][J], t1[I][J], a, b[J]);
         }
@@ -202,7 +254,7 @@ __device__ __forceinline__ void frag_propagate(Ctx<32>& c, const KParams& p, con
 #pragma unroll
       for (int J = 0; J < NB; J++)
         if (nzA(J, K)) {
-          const double b = a_elem(c, 8 * J + g, 8 * K + 4 * kk + t, n);  // A(J,K)^T[4kk+t][g]
+          const double b = a_op(J, K, kk);  // A(J,K)^T[4kk+t][g]
 #pragma unroll
           for (int I = 0; I < NB; I++) dmma(c0[I][J], c1[I][J], a[I], b);
         }
@@ -273,16 +325,19 @@ struct FragCore {
         const int col = H.col[k], J = col >> 3, tt = (col & 7) >> 1;
         const bool e = col & 1;
         double pv[NB];
+#define VIEKF_FRAG_PICK(JJ)                                      \
+  _Pragma("unroll") for (int I = 0; I < NB; I++) pv[I] = e ? c1[I][JJ] : c0[I][JJ];
+        switch (J) {  // uniform over the warp
+          case 0: VIEKF_FRAG_PICK(0) break;
+          case 1: VIEKF_FRAG_PICK(1) break;
+          case 2: VIEKF_FRAG_PICK(2) break;
+          case 3: VIEKF_FRAG_PICK(3) break;
+          default: VIEKF_FRAG_PICK(4) break;
+        }
+#undef VIEKF_FRAG_PICK
+        if (t != tt) {
 #pragma unroll
-        for (int I = 0; I < NB; I++) {
-          double x0 = c0[I][0], x1 = c1[I][0];
-#pragma unroll
-          for (int JJ = 1; JJ < NB; JJ++)
-            if (JJ == J) {
-              x0 = c0[I][JJ];
-              x1 = c1[I][JJ];
-            }
-          pv[I] = (t == tt) ? (e ? x1 : x0) : 0.0;
+          for (int I = 0; I < NB; I++) pv[I] = 0.0;
         }
 #pragma unroll
         for (int I = 0; I < NB; I++)
@@ -475,7 +530,10 @@ __global__ void __launch_bounds__(32 * VIEKF_FRAG_WPC, VIEKF_FRAG_MINB) viekf_fr
       const int np2 = (n0 * (n0 + 1) / 2 + 1) >> 1;
       for (int i = c.tid; i < np2; i += G) sP[i] = gP[i];
     }
-    if (p.ev_count > 0 && c.tid < 8) resolve_values(p, p.ev_first, b, ginst, c.tid, c.sm + SM_ZV);
+    if (c.tid < 6)
+      c.sm[SM_BIAS + c.tid] = (p.seed && p.bias_range[c.tid] != 0.0) ? p.bias_range[c.tid] * viekf_uniform_pm1(p.seed, (uint64_t)ginst, VIEKF_NOISE_EVENT_BIAS, c.tid) : 0.0;
+    __syncwarp();
+    if (p.ev_count > 0 && c.tid < 8) frag_resolve(p, p.ev_first, b, ginst, c.tid, c.sm + SM_BIAS, c.sm + SM_ZV);
     double c0[NB][NB], c1[NB][NB];
     reload(c, 16 + 3 * len0, c0, c1);
     __syncwarp();
@@ -485,7 +543,7 @@ __global__ void __launch_bounds__(32 * VIEKF_FRAG_WPC, VIEKF_FRAG_MINB) viekf_fr
       const int kind = E.kind;
       c.zv = c.sm + SM_ZV + 8 * (int)((e - p.ev_first) & 1);
       if (e + 1 < p.ev_first + p.ev_count && c.tid < 8)
-        resolve_values(p, e + 1, b, ginst, c.tid, c.sm + SM_ZV + 8 * (int)((e + 1 - p.ev_first) & 1));
+        frag_resolve(p, e + 1, b, ginst, c.tid, c.sm + SM_BIAS, c.sm + SM_ZV + 8 * (int)((e + 1 - p.ev_first) & 1));
       int result = VIEKF_MEAS_NONE;
       if (kind == VIEKF_EV_PROP) {
         frag_propagate(c, p, E, c0, c1);
