@@ -187,10 +187,88 @@ __device__ __forceinline__ void frag_resolve(const KParams& p, int64_t e, int64_
 // ------------------------------------------------------------------------------------------------------------------
 // PROP: propagate_state (vi_ekf.cpp:262-318); dynamics, discretisation and boxplus are the shared code
 // ------------------------------------------------------------------------------------------------------------------
+// x <- x [+] d s (vi_ekf_helper.cpp:88-98) on one warp: the 13 additive base components one per lane, then one quaternion item per lane
+// (feature i on lane i, the attitude on lane len), which share the exp / otimes code
+__device__ __forceinline__ void frag_boxplus(double* __restrict__ x, const double* __restrict__ d, double s, int len, int lane) {
+  if (lane < 13) {
+    const int xi = lane < 6 ? lane : lane + 4, di = lane < 6 ? lane : lane + 3;
+    x[xi] = fma(d[di], s, x[xi]);
+  }
+  if (lane <= len) {
+    const bool isb = (lane == len);
+    double* xq = isb ? x + 6 : x + 17 + 5 * lane;
+    const Q4 q = ldq(xq);
+    V3 dv;
+    if (isb) {
+      dv = mk3(d[6] * s, d[7] * s, d[8] * s);
+    } else {
+      const double* df = d + 16 + 3 * lane;
+      const double d0 = df[0] * s, d1 = df[1] * s;
+      const V3 T0 = rota_ex(q), T1 = rota_ey(q);
+      dv = mk3(T0.x * d0 + T1.x * d1, T0.y * d0 + T1.y * d1, T0.z * d0 + T1.z * d1);
+      xq[4] = fma(df[2], s, xq[4]);
+    }
+    const Q4 e = qexp(dv);
+    const Q4 a = isb ? q : e, b = isb ? e : q;  // base: q (x) exp(v); feature: exp(T_zeta d) (x) q
+    stq(xq, otimes(a, b));
+  }
+}
+
+// prop_discretise of viekf_dev.cuh with the rows dealt for one warp: the 3 len feature rows in one pass (one per lane), the base rows in
+// a second (9 non-trivial + 7 identity rows); the shared version's stride-32 deal runs the feature-row code twice at n = 40
+__device__ __forceinline__ bool frag_discretise(Ctx<32>& c, const KParams& p, const viekf_event& E, double& dt_out, int& len_out) {
+  if (c.tid == 0) {
+    const double* zz = c.zv;
+    Q4 qbu = ldq(p.qbu);
+    V3 a = rota(qbu, mk3(zz[0], zz[1], zz[2])), g = rota(qbu, mk3(zz[3], zz[4], zz[5]));
+    double* ul = c.sm + SM_UB;
+    ul[0] = a.x; ul[1] = a.y; ul[2] = a.z; ul[3] = g.x; ul[4] = g.y; ul[5] = g.z;
+  }
+  const int started = c.sc[SC_STARTED];
+  const double tcur = *c.tcur;
+  const double dt = E.t - tcur;
+  if (!started) {
+    __syncwarp();
+    if (c.tid == 0) {
+      c.sc[SC_STARTED] = 1;
+      *c.tcur = E.t;
+    }
+    __syncwarp();
+    return false;
+  }
+  if (fabs(dt) < 1e-6) {
+    __syncwarp();
+    return false;
+  }
+  if (dt < 0) {
+    if (c.tid == 0) c.sc[SC_FLAGS] |= VIEKF_FLAG_BACKWARD_DT;
+    __syncwarp();
+    return false;
+  }
+  const int len = c.sc[SC_LEN];
+  const int n = 16 + 3 * len;
+  const double* zv = c.zv;
+  double ub[6];
+  {
+    Q4 qbu = ldq(p.qbu);
+    V3 a = rota(qbu, mk3(zv[0], zv[1], zv[2])), g = rota(qbu, mk3(zv[3], zv[4], zv[5]));
+    ub[0] = a.x; ub[1] = a.y; ub[2] = a.z; ub[3] = g.x; ub[4] = g.y; ub[5] = g.z;
+  }
+  base_dynamics(c, p, ub);
+  for (int i = c.tid; i < len; i += 32) feature_dynamics(c, p, ub, i);
+  __syncwarp();
+  discretise_rows(c, dt, n, n, 16 + c.tid, 1 << 20);             // feature rows, one per lane (3 len <= 24)
+  discretise_rows(c, dt, n, n, c.tid < 16 ? c.tid : n, 1 << 20);  // base rows
+  __syncwarp();
+  dt_out = dt;
+  len_out = len;
+  return true;
+}
+
 __device__ __forceinline__ void frag_propagate(Ctx<32>& c, const KParams& p, const viekf_event& E, double (&c0)[NB][NB], double (&c1)[NB][NB]) {
   double dt;
   int len;
-  if (!prop_discretise(c, p, E, dt, len, 0)) return;
+  if (!frag_discretise(c, p, E, dt, len)) return;
   const int n = 16 + 3 * len;
   const int lane = c.tid, g = lane >> 2, t = lane & 3;
   const int src0 = (lane & ~3) + (t >> 1), src1 = src0 + 2;
@@ -285,7 +363,7 @@ __device__ __forceinline__ void frag_propagate(Ctx<32>& c, const KParams& p, con
     }
   }
   // ---- state: x <- x [+] xdot dt, time, fix_depth ----
-  boxplus_inplace(c, c.dx, dt, len);
+  frag_boxplus(c.x, c.dx, dt, len, c.tid);
   if (c.tid == 0) *c.tcur = E.t;
   fix_depth(c, p, len, c0, c1);
 }
@@ -431,7 +509,7 @@ struct FragCore {
     if (__any_sync(0xffffffffu, bad)) cols[8] = 1;
     __syncwarp();
     if (!cols[8]) {
-      boxplus_inplace(c, c.dx, 1.0, len);
+      frag_boxplus(c.x, c.dx, 1.0, len, c.tid);
       // ---- P += (1 - a a^T) o (G K^T + K G^T): A operand rows (g0 g1 k0 k1), B operand columns (k0 k1 g0 g1) ----
       double a[NB], b[NB], a2[NB], b2[NB];
 #pragma unroll
