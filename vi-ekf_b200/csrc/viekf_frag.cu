@@ -334,7 +334,7 @@ __device__ __forceinline__ void frag_propagate(Ctx<32>& c, const KParams& p, con
         if (nzA(J, K)) {
           const double b = a_op(J, K, kk);  // A(J,K)^T[4kk+t][g]
 #pragma unroll
-          for (int I = 0; I < NB; I++) dmma(c0[I][J], c1[I][J], a[I], b);
+          for (int I = J; I < NB; I++) dmma(c0[I][J], c1[I][J], a[I], b);  // lower blocks only: symmetrise() rebuilds the upper ones
         }
     }
 #pragma unroll
@@ -351,7 +351,7 @@ __device__ __forceinline__ void frag_propagate(Ctx<32>& c, const KParams& p, con
 #pragma unroll
     for (int I = 0; I < NB; I++)
 #pragma unroll
-      for (int J = 0; J < NB; J++) dmma(c0[I][J], c1[I][J], a[I], b[J]);
+      for (int J = 0; J <= I; J++) dmma(c0[I][J], c1[I][J], a[I], b[J]);
   }
   // process noise on the live diagonal (vi_ekf.cpp:304)
 #pragma unroll
@@ -531,7 +531,7 @@ struct FragCore {
         for (int I = 0; I < NB; I++) {
           const double ai = (8 * I + g < nmax) ? v.av[8 * I + g] : 0.0;
 #pragma unroll
-          for (int J = 0; J < NB; J++) {
+          for (int J = 0; J <= I; J++) {
             double d0 = 0.0, d1 = 0.0;
             dmma(d0, d1, a[I], b[J]);
             if (RD == 3) dmma(d0, d1, a2[I], b2[J]);
@@ -545,7 +545,7 @@ struct FragCore {
 #pragma unroll
         for (int I = 0; I < NB; I++)
 #pragma unroll
-          for (int J = 0; J < NB; J++) {
+          for (int J = 0; J <= I; J++) {
             dmma(c0[I][J], c1[I][J], a[I], b[J]);
             if (RD == 3) dmma(c0[I][J], c1[I][J], a2[I], b2[J]);
           }
