@@ -169,6 +169,8 @@ def kernel_name(n):
     """The executor launch_tape selects for N features (csrc/viekf_kernel.cu group_size_for, csrc/viekf_tile.cu tile_warps_for)."""
     if n == 0 and os.environ.get("VIEKF_GROUP", "8") == "8":
         return "viekf_octet_kernel (N = 0 executor: eight lanes per filter, covariance in registers)"
+    if 1 <= n <= 8 and os.environ.get("VIEKF_GROUP", "2") == "2":
+        return "viekf_frag_kernel (1 <= N <= 8 executor: one warp per filter, covariance in FP64 tensor-core fragments)"
     if 7 <= n <= 14:
         return "viekf_tile_kernel<1,*> (register-tile tape executor, one tile warp)"
     if 15 <= n <= 26:

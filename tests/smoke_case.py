@@ -6,7 +6,7 @@ from tests.common import REL_TOL
 
 
 def run(pkg, verbose=False):
-    """NF = 12 runs on the register-tile executor (the kernel bench.py measures), NF = 6 on the shared-memory executor, NF = 0 on
+    """NF = 12 runs on the register-tile executor (the kernel family bench.py measures), NF = 6 on the fragment executor, NF = 0 on
     the lane-octet executor."""
     worst = (0.0, 0.0)
     for NF in (12, 6, 0):

@@ -4,8 +4,8 @@ through the kernel instantiations that carry the reported numbers:
 
   configs[3]  N = 25  viekf_tile_kernel<3,3>   1000 IMU steps
   configs[4]  N = 35  viekf_tile_kernel<6,2>    200 IMU steps
-  configs[2]  N = 8   viekf_tile_kernel<1,6>   1000 IMU steps
-  configs[1]  N = 0   small-N executor          1000 IMU steps
+  configs[2]  N = 8   viekf_frag_kernel        1000 IMU steps   (and viekf_tile_kernel<1,6>, the round-1 mapping)
+  configs[1]  N = 0   viekf_octet_kernel       1000 IMU steps
 
 Per-event meas_result_t, feature ids, live counts, flags and counters bit-exact; x / P within 1e-9 relative (north_star).
 Instances whose closest gate decision sits within 1e-7 of the threshold are excluded and counted (never re-seeded).
@@ -22,11 +22,12 @@ from tests.test_gpu_parity import _stats_close
 pytestmark = pytest.mark.gpu
 
 SOAK = int(os.environ.get("VIEKF_SOAK", "1"))  # VIEKF_SOAK=k: k times the IMU steps and k times the oracle sample (evidence runs, profiles/)
-CASES = [  # N, B, IMU steps, oracle sample, forced filters per CTA (None = the launcher's own choice at this B)
-    pytest.param(25, 512, 1000 * SOAK, 64 * SOAK, 3, id="configs3_N25_tile33"),
-    pytest.param(35, 304, 200 * SOAK, 32 * SOAK, 2, id="configs4_N35_tile62"),
-    pytest.param(8, 1024, 1000 * SOAK, 64 * SOAK, 6, id="configs2_N8_tile16"),
-    pytest.param(0, 1024, 1000 * SOAK, 64 * SOAK, None, id="configs1_N0_octet"),
+CASES = [  # N, B, IMU steps, oracle sample, forced filters per CTA of the tile executor, forced VIEKF_GROUP (None = the engine's choice)
+    pytest.param(25, 512, 1000 * SOAK, 64 * SOAK, 3, None, id="configs3_N25_tile33"),
+    pytest.param(35, 304, 200 * SOAK, 32 * SOAK, 2, None, id="configs4_N35_tile62"),
+    pytest.param(8, 1024, 1000 * SOAK, 64 * SOAK, None, None, id="configs2_N8_frag"),
+    pytest.param(8, 1024, 1000 * SOAK, 64 * SOAK, 6, 1, id="N8_tile16"),
+    pytest.param(0, 1024, 1000 * SOAK, 64 * SOAK, None, None, id="configs1_N0_octet"),
 ]
 
 
@@ -35,11 +36,13 @@ def _run_oracle(oracle_mod, sim, cfg, N, ev, idp, nb, count):
                                 perturb_seed=sim.BENCH_SEED + 1, n_buckets=nb)
 
 
-@pytest.mark.parametrize("N,B,steps,sample,fpc", CASES)
-def test_bench_tape_parity(pkg, oracle_mod, monkeypatch, N, B, steps, sample, fpc):
+@pytest.mark.parametrize("N,B,steps,sample,fpc,group", CASES)
+def test_bench_tape_parity(pkg, oracle_mod, monkeypatch, N, B, steps, sample, fpc, group):
     sim = pkg.sim
     if fpc is not None:
         monkeypatch.setenv("VIEKF_TILE_FPC", str(fpc))
+    if group is not None:
+        monkeypatch.setenv("VIEKF_GROUP", str(group))
     n_slices = steps // sim.BENCH_IMU_PER_STEP
     cfg, ev, idp, info, slices = sim.bench_workload(N, n_slices)
     nb = info["n_buckets"]

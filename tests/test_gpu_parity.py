@@ -237,9 +237,10 @@ def test_chunked_tape_equals_single_launch(pkg, oracle_mod):
     assert b.launch_count() == len(cuts) - 1
 
 
-@pytest.mark.parametrize("group", [1, 32, 64, 128, 256])
+@pytest.mark.parametrize("group", [1, 2, 32, 64, 128, 256])
 def test_every_thread_group_mapping(pkg, oracle_mod, group, monkeypatch):
-    """The same filter under each threads-per-filter mapping (1 = register-tile executor, warp / 2 warps / CTA) stays within tolerance."""
+    """The same filter under each mapping (1 = register-tile executor, 2 = fragment executor, warp / 2 warps / CTA of the shared-memory
+    executor) stays within tolerance."""
     monkeypatch.setenv("VIEKF_GROUP", str(group))
     cfg = _default_cfg()
     NF = 7

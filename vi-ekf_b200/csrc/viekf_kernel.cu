@@ -26,8 +26,7 @@ size_t smem_bytes_per_filter(int N) { return (size_t)make_layout(N).total * size
 
 int group_size_for(int N) {
   if (N == 0) return GROUP_OCTET;
-  if (N <= 1) return 32;
-  if (N <= 6) return 64;
+  if (N <= 8) return GROUP_FRAG;  // 1 ... 8 features: covariance in tensor-core fragments (VIEKF_GROUP=32 / 64 / 1 select the older mappings)
   if (tile_warps_for(N) > 0) return GROUP_TILE;
   return 128;
 }
