@@ -301,7 +301,7 @@ int viekf_batch_create(const viekf_config* cfg, int64_t B, int32_t N, int32_t de
     if (v == vk::GROUP_OCTET && N == 0) h->group = v;
     if (v == vk::GROUP_FRAG && N >= 1 && N <= 8) h->group = v;
   }
-  const size_t need = (h->group == vk::GROUP_OCTET) ? vk::octet_smem_bytes() : (h->group == vk::GROUP_FRAG) ? vk::smem_bytes_per_filter(N) * vk::frag_filters_per_cta() : (h->group == vk::GROUP_TILE) ? vk::tile_smem_bytes(N)
+  const size_t need = (h->group == vk::GROUP_OCTET) ? vk::octet_smem_bytes() : (h->group == vk::GROUP_FRAG) ? vk::frag_smem_bytes(N) : (h->group == vk::GROUP_TILE) ? vk::tile_smem_bytes(N)
                                                    : vk::smem_bytes_per_filter(N) * vk::smem_filters_per_cta(h->group);
   if (need > (size_t)prop.sharedMemPerBlockOptin) {
     delete h;

@@ -67,7 +67,7 @@ static const int GROUP_TILE = 1;
 static const int GROUP_OCTET = 8;
 // GROUP_FRAG selects the 1 <= N <= 8 executor with the covariance in FP64 tensor-core fragments, one warp per filter (viekf_frag.cu)
 static const int GROUP_FRAG = 2;
-int frag_filters_per_cta();
+size_t frag_smem_bytes(int N);
 cudaError_t launch_frag(const KParams& p, int sm_count, cudaStream_t stream);
 size_t octet_smem_bytes();
 cudaError_t launch_octet(const KParams& p, int sm_count, cudaStream_t stream);

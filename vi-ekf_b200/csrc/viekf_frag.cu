@@ -21,12 +21,6 @@
 
 namespace vk {
 
-#ifndef VIEKF_FRAG_WPC
-#define VIEKF_FRAG_WPC 4  // filters (= warps) per CTA, in event lock-step
-#endif
-#ifndef VIEKF_FRAG_MINB
-#define VIEKF_FRAG_MINB 2
-#endif
 
 namespace frg {
 constexpr int NB = 5;  // 8 x 8 blocks per side: n <= 40
@@ -165,8 +159,7 @@ using namespace frg;
 
 // resolve_values of viekf_dev.cuh with the instance's constant IMU bias taken from a per-slice cache (sm[SM_BIAS .. +5])
 enum { SM_BIAS = 62 };
-__device__ __forceinline__ void frag_resolve(const KParams& p, int64_t e, int64_t b, int64_t ginst, int k, const double* bias, double* out) {
-  const viekf_event& E = p.ev[e];
+__device__ __forceinline__ void frag_resolve(const KParams& p, const viekf_event& E, int64_t e, int64_t b, int64_t ginst, int k, const double* bias, double* out) {
   const int kind = E.kind;
   if (!(kind == VIEKF_EV_PROP || kind == VIEKF_EV_UPD || kind == VIEKF_EV_INIT)) return;
   double v = (E.noise >= 0 && p.values) ? p.values[b * p.vstride + 8 * (int64_t)E.noise + k] : E.z[k];
@@ -512,14 +505,15 @@ struct FragCore {
       frag_boxplus(c.x, c.dx, 1.0, len, c.tid);
       // ---- P += (1 - a a^T) o (G K^T + K G^T): A operand rows (g0 g1 k0 k1), B operand columns (k0 k1 g0 g1) ----
       double a[NB], b[NB], a2[NB], b2[NB];
+      // element t of the rows (g0 g1 k0 k1) / (k0 k1 g0 g1): the vectors are the interleaved pairs Kv / KSv of the update workspace
+      const double* wA = c.upd + ((t < 2) ? 4 * nmax : 0) + (t & 1);
+      const double* wB = c.upd + ((t < 2) ? 0 : 4 * nmax) + (t & 1);
 #pragma unroll
       for (int I = 0; I < NB; I++) {
         const int r = 8 * I + g;
         const bool in = r < nmax;
-        const double2 zero2 = make_double2(0.0, 0.0);
-        const double2 gI = in ? v.KSv[r] : zero2, kI = in ? v.Kv[r] : zero2;
-        a[I] = t == 0 ? gI.x : t == 1 ? gI.y : t == 2 ? kI.x : kI.y;
-        b[I] = t == 0 ? kI.x : t == 1 ? kI.y : t == 2 ? gI.x : gI.y;
+        a[I] = in ? wA[2 * r] : 0.0;
+        b[I] = in ? wB[2 * r] : 0.0;
         if (RD == 3) {
           const double g2 = in ? v.KS2[r] : 0.0, k2 = in ? v.K2[r] : 0.0;
           a2[I] = t == 0 ? g2 : t == 2 ? k2 : 0.0;
@@ -562,9 +556,10 @@ struct FragCore {
 // ------------------------------------------------------------------------------------------------------------------
 // the persistent tape executor (skeleton of viekf_tape_kernel<32>: same shared-memory block per filter, same load / store)
 // ------------------------------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(32 * VIEKF_FRAG_WPC, VIEKF_FRAG_MINB) viekf_frag_kernel(const __grid_constant__ KParams p) {
+template <int WPC>
+__global__ void __launch_bounds__(32 * WPC, 8 / WPC) viekf_frag_kernel(const __grid_constant__ KParams p) {
   extern __shared__ __align__(16) double smem[];
-  constexpr int G = 32, GPC = VIEKF_FRAG_WPC;
+  constexpr int G = 32, GPC = WPC;
   const Layout L = make_layout(p.N);
   Ctx<32> c;
   c.gi = threadIdx.x / G;
@@ -577,6 +572,8 @@ __global__ void __launch_bounds__(32 * VIEKF_FRAG_WPC, VIEKF_FRAG_MINB) viekf_fr
   c.rm = c.ids + p.N;
   c.sc = c.rm + p.N;
   c.tcur = c.sm + SM_T;
+  double* evb = smem + (size_t)GPC * L.total + c.gi * 96;
+  static_assert(sizeof(viekf_event) == 31 * sizeof(double), "event staging assumes 31 doubles per record");
   const int nmax = 16 + 3 * p.N;
   for (int i = c.tid; i < nmax; i += G) c.lam[i] = (i < 16) ? p.lam[i] : p.lamf[(i - 16) % 3];
   for (int64_t b0 = (int64_t)blockIdx.x * GPC; b0 < p.B; b0 += (int64_t)gridDim.x * GPC) {
@@ -611,17 +608,27 @@ __global__ void __launch_bounds__(32 * VIEKF_FRAG_WPC, VIEKF_FRAG_MINB) viekf_fr
     if (c.tid < 6)
       c.sm[SM_BIAS + c.tid] = (p.seed && p.bias_range[c.tid] != 0.0) ? p.bias_range[c.tid] * viekf_uniform_pm1(p.seed, (uint64_t)ginst, VIEKF_NOISE_EVENT_BIAS, c.tid) : 0.0;
     __syncwarp();
-    if (p.ev_count > 0 && c.tid < 8) frag_resolve(p, p.ev_first, b, ginst, c.tid, c.sm + SM_BIAS, c.sm + SM_ZV);
+    // the event records are staged three deep in shared memory (this event, the next one for the value resolution, one in flight)
+    if (c.tid < 31) {
+      if (p.ev_count > 0) evb[c.tid] = ((const double*)(p.ev + p.ev_first))[c.tid];
+      if (p.ev_count > 1) evb[32 + c.tid] = ((const double*)(p.ev + p.ev_first + 1))[c.tid];
+    }
+    __syncwarp();
+    if (p.ev_count > 0 && c.tid < 8) frag_resolve(p, *(const viekf_event*)evb, p.ev_first, b, ginst, c.tid, c.sm + SM_BIAS, c.sm + SM_ZV);
     double c0[NB][NB], c1[NB][NB];
     reload(c, 16 + 3 * len0, c0, c1);
     __syncwarp();
     // ---- run the tape slice ----
-    for (int64_t e = p.ev_first; e < p.ev_first + p.ev_count; e++) {
-      const viekf_event& E = p.ev[e];
+    for (int64_t rel = 0; rel < p.ev_count; rel++) {
+      const int64_t e = p.ev_first + rel;
+      const viekf_event& E = *(const viekf_event*)(evb + 32 * (int)(rel % 3));
+      const bool stage = rel + 2 < p.ev_count && c.tid < 31;
+      double ev_next = 0.0;
+      if (stage) ev_next = ((const double*)(p.ev + e + 2))[c.tid];
       const int kind = E.kind;
-      c.zv = c.sm + SM_ZV + 8 * (int)((e - p.ev_first) & 1);
-      if (e + 1 < p.ev_first + p.ev_count && c.tid < 8)
-        frag_resolve(p, e + 1, b, ginst, c.tid, c.sm + SM_BIAS, c.sm + SM_ZV + 8 * (int)((e + 1 - p.ev_first) & 1));
+      c.zv = c.sm + SM_ZV + 8 * (int)(rel & 1);
+      if (rel + 1 < p.ev_count && c.tid < 8)
+        frag_resolve(p, *(const viekf_event*)(evb + 32 * (int)((rel + 1) % 3)), e + 1, b, ginst, c.tid, c.sm + SM_BIAS, c.sm + SM_ZV + 8 * (int)((rel + 1) & 1));
       int result = VIEKF_MEAS_NONE;
       if (kind == VIEKF_EV_PROP) {
         frag_propagate(c, p, E, c0, c1);
@@ -654,6 +661,7 @@ __global__ void __launch_bounds__(32 * VIEKF_FRAG_WPC, VIEKF_FRAG_MINB) viekf_fr
         }
         reload(c, 16 + 3 * c.sc[SC_LEN], c0, c1);
       }
+      if (stage) evb[32 * (int)((rel + 2) % 3) + c.tid] = ev_next;
       __syncthreads();
       if (p.results && c.tid == 0 && b >= p.res_first && b < p.res_first + p.res_count)
         p.results[(b - p.res_first) * p.n_events + e] = (uint8_t)result;
@@ -683,26 +691,33 @@ __global__ void __launch_bounds__(32 * VIEKF_FRAG_WPC, VIEKF_FRAG_MINB) viekf_fr
   }
 }
 
-int frag_filters_per_cta() { return VIEKF_FRAG_WPC; }
+// filters (= warps) per CTA, in event lock-step.  Eight warps fit an SM (255 registers): as ONE CTA they share the instruction stream
+// (N >= 7: 39 M against 36 M filter-steps/s as two CTAs of four); for smaller N two CTAs of four are faster (47 M against 45 M at N = 4)
+static int frag_wpc(int N) { return N >= 7 ? 8 : 4; }
+size_t frag_smem_bytes(int N) { return (smem_bytes_per_filter(N) + 96 * sizeof(double)) * frag_wpc(N); }
 
-cudaError_t launch_frag(const KParams& p, int sm_count, cudaStream_t stream) {
-  if (p.N < 1 || p.N > 8) return cudaErrorInvalidValue;
-  constexpr int GPC = VIEKF_FRAG_WPC;
-  const size_t smem = smem_bytes_per_filter(p.N) * GPC;
-  cudaError_t e = cudaFuncSetAttribute(viekf_frag_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+template <int WPC>
+static cudaError_t launch_frag_wpc(const KParams& p, int sm_count, cudaStream_t stream) {
+  const size_t smem = frag_smem_bytes(p.N);
+  cudaError_t e = cudaFuncSetAttribute(viekf_frag_kernel<WPC>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   if (e != cudaSuccess) return e;
-  e = cudaFuncSetAttribute(viekf_frag_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, (int)cudaSharedmemCarveoutMaxShared);
+  e = cudaFuncSetAttribute(viekf_frag_kernel<WPC>, cudaFuncAttributePreferredSharedMemoryCarveout, (int)cudaSharedmemCarveoutMaxShared);
   if (e != cudaSuccess) return e;
   int occ = 0;
-  e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, viekf_frag_kernel, 32 * GPC, smem);
+  e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, viekf_frag_kernel<WPC>, 32 * WPC, smem);
   if (e != cudaSuccess) return e;
   if (occ < 1) return cudaErrorInvalidConfiguration;
-  const int64_t need = (p.B + GPC - 1) / GPC;
+  const int64_t need = (p.B + WPC - 1) / WPC;
   int64_t grid = (int64_t)sm_count * occ;  // persistent: a whole number of waves of the SM count
   if (need < grid) grid = need;
   if (grid < 1) grid = 1;
-  viekf_frag_kernel<<<(unsigned)grid, 32 * GPC, smem, stream>>>(p);
+  viekf_frag_kernel<WPC><<<(unsigned)grid, 32 * WPC, smem, stream>>>(p);
   return cudaGetLastError();
+}
+
+cudaError_t launch_frag(const KParams& p, int sm_count, cudaStream_t stream) {
+  if (p.N < 1 || p.N > 8) return cudaErrorInvalidValue;
+  return frag_wpc(p.N) == 8 ? launch_frag_wpc<8>(p, sm_count, stream) : launch_frag_wpc<4>(p, sm_count, stream);
 }
 
 }  // namespace vk
