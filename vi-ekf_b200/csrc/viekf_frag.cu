@@ -73,7 +73,8 @@ __device__ __forceinline__ void reload(const Ctx<32>& c, int n, double (&c0)[NB]
 }
 // upper triangle := transpose of the lower one: destination element (g, 2t + e) of block (J, I) is element (2t + e, g) of block
 // (I, J), in lane 4 (2t + e) + g / 2, register g % 2
-__device__ __forceinline__ void symmetrise(int lane, double (&c0)[NB][NB], double (&c1)[NB][NB]) {
+template <bool FULL>
+__device__ __forceinline__ void symmetrise(int lane, int nbl, double (&c0)[NB][NB], double (&c1)[NB][NB]) {
   const int g = lane >> 2, t = lane & 3;
   const int sa = 8 * t + (g >> 1), sb = sa + 4;
   const bool odd = g & 1;
@@ -81,6 +82,7 @@ __device__ __forceinline__ void symmetrise(int lane, double (&c0)[NB][NB], doubl
   for (int I = 0; I < NB; I++)
 #pragma unroll
     for (int J = 0; J <= I; J++) {
+      if (!FULL && I >= nbl) continue;  // dead blocks are zero on both sides (uniform over the warp)
       const double x00 = __shfl_sync(0xffffffffu, c0[I][J], sa), x01 = __shfl_sync(0xffffffffu, c1[I][J], sa);
       const double x10 = __shfl_sync(0xffffffffu, c0[I][J], sb), x11 = __shfl_sync(0xffffffffu, c1[I][J], sb);
       const double t0 = odd ? x01 : x00, t1 = odd ? x11 : x10;
@@ -258,14 +260,15 @@ __device__ __forceinline__ bool frag_discretise(Ctx<32>& c, const KParams& p, co
   return true;
 }
 
+// FULL: no live-block guards (N >= 6: nearly every block is live and the branches around the DMMAs cost 9 % at N = 8)
+template <bool FULL>
 __device__ __forceinline__ void frag_propagate(Ctx<32>& c, const KParams& p, const viekf_event& E, double (&c0)[NB][NB], double (&c1)[NB][NB]) {
   double dt;
   int len;
   if (!frag_discretise(c, p, E, dt, len)) return;
   const int n = 16 + 3 * len;
+  const int nbl = (n + 7) >> 3;  // live 8 x 8 blocks per side
   const int lane = c.tid, g = lane >> 2, t = lane & 3;
-  const int src0 = (lane & ~3) + (t >> 1), src1 = src0 + 2;
-  const bool odd = t & 1;
   // dense copy of blkdiag(A_ff) (3N x 3N, row stride 3N) so that every operand element of A is one load off a per-lane row base:
   // in the packed-P area (stale while the fragments hold P) at N = 8, in the AbT | T arrays (unused by this executor) below
   const int S = 3 * p.N;
@@ -279,9 +282,12 @@ __device__ __forceinline__ void frag_propagate(Ctx<32>& c, const KParams& p, con
       for (int k = 0; k < 3; k++) Aff[(3 * lane + a) * S + 3 * lane + k] = c.Afd[(3 * lane + a) * 19 + 16 + k];
   }
   __syncwarp();
-  // A(8I + g, 8K + 4kk + t): rows < 16 from Abd, feature rows from Afd (base columns) / Aff (feature columns); dead rows are zero
+  // The inner index of an 8 x 8 x 8 block product is summed in the order (0 2 4 6 | 1 3 5 7): the lane (g, t) then contributes columns
+  // 2t and 2t + 1 of an accumulator block -- exactly the two elements it holds -- so an accumulator block is an A operand (and, through
+  // the symmetry of P, a B operand) WITHOUT any shuffle; the other operand, read from shared memory, is indexed to match:
+  // A(8I + g, 8K + 2t + kk): rows < 16 from Abd, feature rows from Afd (base columns) / Aff (feature columns); dead rows are zero
   auto a_op = [&](int I, int K, int kk) -> double {
-    const int col = 8 * K + 4 * kk + t;
+    const int col = 8 * K + 2 * t + kk;
     if (I < 2) return c.Abd[(8 * I + g) * 16 + col];  // K < 2 here
     const int fr = 8 * (I - 2) + g;
     if (fr >= 3 * len) return 0.0;
@@ -289,7 +295,7 @@ __device__ __forceinline__ void frag_propagate(Ctx<32>& c, const KParams& p, con
     const int fc = col - 16;
     return fc < S ? Aff[fr * S + fc] : 0.0;
   };
-  // ---- T = A P ----
+  // ---- T = A P: B operand P(K,J)[2t + kk][g] = P(J,K)[g][2t + kk], the lane's own element of the mirror block ----
   double t0[NB][NB], t1[NB][NB];
 #pragma unroll
   for (int I = 0; I < NB; I++)
@@ -298,19 +304,16 @@ __device__ __forceinline__ void frag_propagate(Ctx<32>& c, const KParams& p, con
 #pragma unroll
   for (int K = 0; K < NB; K++)
 #pragma unroll
-    for (int kk = 0; kk < 2; kk++) {
-      double b[NB];
-#pragma unroll
-      for (int J = 0; J < NB; J++) b[J] = frag_elem(c0[J][K], c1[J][K], kk ? src1 : src0, odd);  // P(K,J)[4kk+t][g] = P(J,K)[g][4kk+t]
+    for (int kk = 0; kk < 2; kk++)
 #pragma unroll
       for (int I = 0; I < NB; I++)
-        if (nzA(I, K)) {
+        if (nzA(I, K) && (FULL || (I < nbl && K < nbl))) {  // blocks behind the live prefix are zero (uniform over the warp)
           const double a = a_op(I, K, kk);
 #pragma unroll
-          for (int J = 0; J < NB; J++) dmma(t0[I][J], t1[I][J], a, b[J]);
+          for (int J = 0; J < NB; J++)
+            if (FULL || J < nbl) dmma(t0[I][J], t1[I][J], a, kk ? c1[J][K] : c0[J][K]);
         }
-    }
-  // ---- P' = T A^T + (G_d Qu) G_d^T (overwrites P) ----
+  // ---- P' = T A^T + (G_d Qu) G_d^T (overwrites P): A operand T(I,K)[g][2t + kk], the lane's own element ----
 #pragma unroll
   for (int I = 0; I < NB; I++)
 #pragma unroll
@@ -318,18 +321,15 @@ __device__ __forceinline__ void frag_propagate(Ctx<32>& c, const KParams& p, con
 #pragma unroll
   for (int K = 0; K < NB; K++)
 #pragma unroll
-    for (int kk = 0; kk < 2; kk++) {
-      double a[NB];
-#pragma unroll
-      for (int I = 0; I < NB; I++) a[I] = frag_elem(t0[I][K], t1[I][K], kk ? src1 : src0, odd);
+    for (int kk = 0; kk < 2; kk++)
 #pragma unroll
       for (int J = 0; J < NB; J++)
-        if (nzA(J, K)) {
-          const double b = a_op(J, K, kk);  // A(J,K)^T[4kk+t][g]
+        if (nzA(J, K) && (FULL || (J < nbl && K < nbl))) {
+          const double b = a_op(J, K, kk);  // A(J,K)^T[2t + kk][g]
 #pragma unroll
-          for (int I = J; I < NB; I++) dmma(c0[I][J], c1[I][J], a[I], b);  // lower blocks only: symmetrise() rebuilds the upper ones
+          for (int I = J; I < NB; I++)
+            if (FULL || I < nbl) dmma(c0[I][J], c1[I][J], kk ? t1[I][K] : t0[I][K], b);  // lower blocks only: symmetrise() rebuilds the upper ones
         }
-    }
 #pragma unroll
   for (int kk = 0; kk < 2; kk++) {
     const int q = 4 * kk + t;
@@ -344,7 +344,8 @@ __device__ __forceinline__ void frag_propagate(Ctx<32>& c, const KParams& p, con
 #pragma unroll
     for (int I = 0; I < NB; I++)
 #pragma unroll
-      for (int J = 0; J <= I; J++) dmma(c0[I][J], c1[I][J], a[I], b[J]);
+      for (int J = 0; J <= I; J++)
+        if (FULL || I < nbl) dmma(c0[I][J], c1[I][J], a[I], b[J]);
   }
   // process noise on the live diagonal (vi_ekf.cpp:304)
 #pragma unroll
@@ -364,6 +365,7 @@ __device__ __forceinline__ void frag_propagate(Ctx<32>& c, const KParams& p, con
 // ------------------------------------------------------------------------------------------------------------------
 // UPD: the covariance-touching part of update() behind ev_update of viekf_dev.cuh (vi_ekf_meas.cpp:226-278)
 // ------------------------------------------------------------------------------------------------------------------
+template <bool FULL>
 struct FragCore {
   Ctx<32>& c;
   const KParams& p;
@@ -385,6 +387,7 @@ struct FragCore {
     const int lane = c.tid, g = lane >> 2, t = lane & 3;
     int* cols = c.sc + SC_COUNT;
     const int nmax = 16 + 3 * p.N;  // rows of the update workspace (the fragment grid covers 40)
+    const int nbl = (n + 7) >> 3;   // live 8 x 8 blocks per side
     UpdVec<32> v(c, nmax);
     // ---- P H^T: the owners of the <= 6 non-zero columns scale their elements, the quad sums ----
     double acc[NB][3];
@@ -526,6 +529,7 @@ struct FragCore {
           const double ai = (8 * I + g < nmax) ? v.av[8 * I + g] : 0.0;
 #pragma unroll
           for (int J = 0; J <= I; J++) {
+            if (!FULL && I >= nbl) continue;
             double d0 = 0.0, d1 = 0.0;
             dmma(d0, d1, a[I], b[J]);
             if (RD == 3) dmma(d0, d1, a2[I], b2[J]);
@@ -540,6 +544,7 @@ struct FragCore {
         for (int I = 0; I < NB; I++)
 #pragma unroll
           for (int J = 0; J <= I; J++) {
+            if (!FULL && I >= nbl) continue;
             dmma(c0[I][J], c1[I][J], a[I], b[J]);
             if (RD == 3) dmma(c0[I][J], c1[I][J], a2[I], b2[J]);
           }
@@ -556,7 +561,7 @@ struct FragCore {
 // ------------------------------------------------------------------------------------------------------------------
 // the persistent tape executor (skeleton of viekf_tape_kernel<32>: same shared-memory block per filter, same load / store)
 // ------------------------------------------------------------------------------------------------------------------
-template <int WPC>
+template <int WPC, bool FULL>
 __global__ void __launch_bounds__(32 * WPC, 8 / WPC) viekf_frag_kernel(const __grid_constant__ KParams p) {
   extern __shared__ __align__(16) double smem[];
   constexpr int G = 32, GPC = WPC;
@@ -631,12 +636,12 @@ __global__ void __launch_bounds__(32 * WPC, 8 / WPC) viekf_frag_kernel(const __g
         frag_resolve(p, *(const viekf_event*)(evb + 32 * (int)((rel + 1) % 3)), e + 1, b, ginst, c.tid, c.sm + SM_BIAS, c.sm + SM_ZV + 8 * (int)((rel + 1) & 1));
       int result = VIEKF_MEAS_NONE;
       if (kind == VIEKF_EV_PROP) {
-        frag_propagate(c, p, E, c0, c1);
-        symmetrise(c.tid, c0, c1);
+        frag_propagate<FULL>(c, p, E, c0, c1);
+        symmetrise<FULL>(c.tid, (16 + 3 * c.sc[SC_LEN] + 7) >> 3, c0, c1);
       } else if (kind == VIEKF_EV_UPD) {
-        FragCore core{c, p, c0, c1};
+        FragCore<FULL> core{c, p, c0, c1};
         result = ev_update(c, p, E, core);
-        symmetrise(c.tid, c0, c1);
+        symmetrise<FULL>(c.tid, (16 + 3 * c.sc[SC_LEN] + 7) >> 3, c0, c1);
       } else {
         // events that touch the covariance element by element run the shared code on the packed copy
         spill(c, 16 + 3 * c.sc[SC_LEN], c0, c1);
@@ -692,32 +697,32 @@ __global__ void __launch_bounds__(32 * WPC, 8 / WPC) viekf_frag_kernel(const __g
 }
 
 // filters (= warps) per CTA, in event lock-step.  Eight warps fit an SM (255 registers): as ONE CTA they share the instruction stream
-// (N >= 7: 39 M against 36 M filter-steps/s as two CTAs of four); for smaller N two CTAs of four are faster (47 M against 45 M at N = 4)
-static int frag_wpc(int N) { return N >= 7 ? 8 : 4; }
+// (40 M against 36 M filter-steps/s as two CTAs of four at N = 8, 46.7 M against 43.3 M at N = 4)
+static int frag_wpc(int N) { return 8; }
 size_t frag_smem_bytes(int N) { return (smem_bytes_per_filter(N) + 96 * sizeof(double)) * frag_wpc(N); }
 
-template <int WPC>
+template <int WPC, bool FULL>
 static cudaError_t launch_frag_wpc(const KParams& p, int sm_count, cudaStream_t stream) {
   const size_t smem = frag_smem_bytes(p.N);
-  cudaError_t e = cudaFuncSetAttribute(viekf_frag_kernel<WPC>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  cudaError_t e = cudaFuncSetAttribute(viekf_frag_kernel<WPC, FULL>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   if (e != cudaSuccess) return e;
-  e = cudaFuncSetAttribute(viekf_frag_kernel<WPC>, cudaFuncAttributePreferredSharedMemoryCarveout, (int)cudaSharedmemCarveoutMaxShared);
+  e = cudaFuncSetAttribute(viekf_frag_kernel<WPC, FULL>, cudaFuncAttributePreferredSharedMemoryCarveout, (int)cudaSharedmemCarveoutMaxShared);
   if (e != cudaSuccess) return e;
   int occ = 0;
-  e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, viekf_frag_kernel<WPC>, 32 * WPC, smem);
+  e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, viekf_frag_kernel<WPC, FULL>, 32 * WPC, smem);
   if (e != cudaSuccess) return e;
   if (occ < 1) return cudaErrorInvalidConfiguration;
   const int64_t need = (p.B + WPC - 1) / WPC;
   int64_t grid = (int64_t)sm_count * occ;  // persistent: a whole number of waves of the SM count
   if (need < grid) grid = need;
   if (grid < 1) grid = 1;
-  viekf_frag_kernel<WPC><<<(unsigned)grid, 32 * WPC, smem, stream>>>(p);
+  viekf_frag_kernel<WPC, FULL><<<(unsigned)grid, 32 * WPC, smem, stream>>>(p);
   return cudaGetLastError();
 }
 
 cudaError_t launch_frag(const KParams& p, int sm_count, cudaStream_t stream) {
   if (p.N < 1 || p.N > 8) return cudaErrorInvalidValue;
-  return frag_wpc(p.N) == 8 ? launch_frag_wpc<8>(p, sm_count, stream) : launch_frag_wpc<4>(p, sm_count, stream);
+  return p.N >= 6 ? launch_frag_wpc<8, true>(p, sm_count, stream) : launch_frag_wpc<8, false>(p, sm_count, stream);
 }
 
 }  // namespace vk
