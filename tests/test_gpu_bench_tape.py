@@ -27,6 +27,7 @@ CASES = [  # N, B, IMU steps, oracle sample, forced filters per CTA of the tile 
     pytest.param(35, 304, 200 * SOAK, 32 * SOAK, 2, None, id="configs4_N35_tile62"),
     pytest.param(8, 1024, 1000 * SOAK, 64 * SOAK, None, None, id="configs2_N8_frag"),
     pytest.param(8, 1024, 1000 * SOAK, 64 * SOAK, 6, 1, id="N8_tile16"),
+    pytest.param(4, 1024, 1000 * SOAK, 64 * SOAK, None, None, id="N4_frag_live_block_guards"),
     pytest.param(0, 1024, 1000 * SOAK, 64 * SOAK, None, None, id="configs1_N0_octet"),
 ]
 
