@@ -161,7 +161,8 @@ using namespace frg;
 
 // resolve_values of viekf_dev.cuh with the instance's constant IMU bias taken from a per-slice cache (sm[SM_BIAS .. +5])
 enum { SM_BIAS = 62 };
-__device__ __forceinline__ void frag_resolve(const KParams& p, const viekf_event& E, int64_t e, int64_t b, int64_t ginst, int k, const double* bias, double* out) {
+__device__ __forceinline__ void frag_resolve(const KParams& p, int64_t e, int64_t b, int64_t ginst, int k, const double* bias, double* out) {
+  const viekf_event& E = p.ev[e];
   const int kind = E.kind;
   if (!(kind == VIEKF_EV_PROP || kind == VIEKF_EV_UPD || kind == VIEKF_EV_INIT)) return;
   double v = (E.noise >= 0 && p.values) ? p.values[b * p.vstride + 8 * (int64_t)E.noise + k] : E.z[k];
@@ -619,7 +620,13 @@ __global__ void __launch_bounds__(32 * WPC, 8 / WPC) viekf_frag_kernel(const __g
       if (p.ev_count > 1) evb[32 + c.tid] = ((const double*)(p.ev + p.ev_first + 1))[c.tid];
     }
     __syncwarp();
-    if (p.ev_count > 0 && c.tid < 8) frag_resolve(p, *(const viekf_event*)evb, p.ev_first, b, ginst, c.tid, c.sm + SM_BIAS, c.sm + SM_ZV);
+    // per-instance values are resolved four events at a time by the whole warp (8 lanes per event) into a ring of eight blocks
+    // (the tail of the T array, which this executor does not use otherwise): one ~300-instruction Philox / Box-Muller pass per four events
+    double* zring = c.T + 192;
+    {
+      const int64_t r = c.tid >> 3;
+      if (r < p.ev_count) frag_resolve(p, p.ev_first + r, b, ginst, c.tid & 7, c.sm + SM_BIAS, zring + 8 * (int)(r & 7));
+    }
     double c0[NB][NB], c1[NB][NB];
     reload(c, 16 + 3 * len0, c0, c1);
     __syncwarp();
@@ -631,9 +638,11 @@ __global__ void __launch_bounds__(32 * WPC, 8 / WPC) viekf_frag_kernel(const __g
       double ev_next = 0.0;
       if (stage) ev_next = ((const double*)(p.ev + e + 2))[c.tid];
       const int kind = E.kind;
-      c.zv = c.sm + SM_ZV + 8 * (int)(rel & 1);
-      if (rel + 1 < p.ev_count && c.tid < 8)
-        frag_resolve(p, *(const viekf_event*)(evb + 32 * (int)((rel + 1) % 3)), e + 1, b, ginst, c.tid, c.sm + SM_BIAS, c.sm + SM_ZV + 8 * (int)((rel + 1) & 1));
+      c.zv = zring + 8 * (int)(rel & 7);
+      if ((rel & 3) == 0) {
+        const int64_t r = rel + 4 + (c.tid >> 3);
+        if (r < p.ev_count) frag_resolve(p, p.ev_first + r, b, ginst, c.tid & 7, c.sm + SM_BIAS, zring + 8 * (int)(r & 7));
+      }
       int result = VIEKF_MEAS_NONE;
       if (kind == VIEKF_EV_PROP) {
         frag_propagate<FULL>(c, p, E, c0, c1);
