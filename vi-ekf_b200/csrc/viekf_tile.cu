@@ -1420,7 +1420,10 @@ __global__ void __launch_bounds__(32 * (TW + 1) * FPC, (384 / (32 * (TW + 1) * F
   const int gi = threadIdx.x / G;
   // warp w of the CTA issues on SM sub-partition w % 4: when G is a multiple of 128 the x warps of all filters of the CTA would
   // share one sub-partition; rotating the roles by the filter index spreads them
-  const int tid = (G % 128 == 0) ? (int)((threadIdx.x % G) + 32 * gi) % G : (int)(threadIdx.x % G);
+#ifndef VIEKF_TILE_ROT
+#define VIEKF_TILE_ROT 1
+#endif
+  const int tid = (G % 128 == 0 && VIEKF_TILE_ROT) ? (int)((threadIdx.x % G) + 32 * gi) % G : (int)(threadIdx.x % G);
   double* base = smem + gi * L.total;
   if ((tid >> 5) == TW) {
     x_role<TW, FPC>(p, base, gi, tid & 31);
